@@ -1,0 +1,141 @@
+/*
+ * nm03.h — C ABI of the B200-native per-slice brain-MRI pipeline (libnm03.so).
+ *
+ * This is the drop-in boundary for the ONE hot path of calebhabesh/NM03-Capstone-Project:
+ * processSingleImage() — import → IntensityNormalization → IntensityClipping → VectorMedianFilter →
+ * ImageSharpening → SeededRegionGrowing (adaptive seeds) → ImageCaster → Dilation (+ Erosion in the
+ * test path).  Reference call sites: src/sequential/main_sequential.cpp:170-272,
+ * src/parallel/main_parallel.cpp:66-170, src/test/test_pipeline.cpp:33-125.  In the reference each
+ * stage is a FAST ProcessObject (`T::create(..)->connect(..)->update()`); the entry points below are
+ * what a binding of that operator API for this path calls instead.  The C++17 shim
+ * (nm03-capstone-project_b200/host/nm03.hpp) re-creates the FAST-shaped classes on top of this ABI.
+ *
+ * Conventions: plain pointers and sizes; every function returns 0 (NM03_OK) or a negative
+ * nm03_status; nothing throws across the ABI; nm03_last_error() gives a thread-local message.
+ * All buffers are caller-owned.  Images are row-major, one channel.  Entry points taking host
+ * buffers copy to/from the GPU themselves; `_device` entry points take device pointers that live
+ * on the context's GPU.  A context may be used from many host threads at once (the reference runs
+ * 16 OpenMP threads, main_parallel.cpp:336-343,401): calls are serialised per stream slot inside.
+ * There is no CPU fallback: without a CUDA device nm03_init fails.
+ */
+#ifndef NM03_H
+#define NM03_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum nm03_status {
+  NM03_OK = 0,
+  NM03_ERR_INVALID = -1,       /* bad argument (null pointer, negative size ...) */
+  NM03_ERR_TOO_SMALL = -2,     /* width or height < 100: main_sequential.cpp:189-192 */
+  NM03_ERR_PARAM = -3,         /* FAST would throw: even / <=2 morphology size, even median window ... */
+  NM03_ERR_NO_SEEDS = -4,      /* SeededRegionGrowing without seed points */
+  NM03_ERR_SEED_OOB = -5,      /* seed point outside the image */
+  NM03_ERR_UNSUPPORTED = -6,   /* valid in FAST, not implemented here (stated in the message) */
+  NM03_ERR_TOO_LARGE = -7,     /* slice exceeds what one thread-block cluster can keep on chip */
+  NM03_ERR_CUDA = -8,          /* CUDA runtime error (message has the detail) */
+  NM03_ERR_NO_DEVICE = -9,
+  NM03_ERR_NOMEM = -10
+} nm03_status;
+
+/* switch values for the details of FAST that cannot be verified offline */
+enum { NM03_BORDER_CLAMP = 0, NM03_BORDER_ZERO = 1 };
+enum { NM03_RG_OPENCL = 0, NM03_RG_HOST = 1 };
+enum { NM03_SE_DISC = 0, NM03_SE_SQUARE = 1 };
+enum { NM03_MORPH_DILATE = 0, NM03_MORPH_ERODE = 1 };
+
+/* Every literal of the reference pipeline in one POD (the reference hard-codes them). */
+typedef struct nm03_params {
+  float norm_low, norm_high, norm_min, norm_max; /* IntensityNormalization::create(0.5f,2.5f,0.0f,10000.0f) main_sequential.cpp:195-196 */
+  float clip_min, clip_max;                      /* IntensityClipping::create(0.68f,4000.0f)     main_sequential.cpp:200 */
+  int median_window;                             /* VectorMedianFilter::create(7)                main_sequential.cpp:204 */
+  float sharpen_gain, sharpen_sigma;             /* ImageSharpening::create(2.0f,0.5f,9)         main_sequential.cpp:208 */
+  int sharpen_mask;
+  float rg_min, rg_max;                          /* SeededRegionGrowing::create(0.74f,0.91f,..)  main_sequential.cpp:232-233 */
+  int dilate_size;                               /* Dilation::create(3)                          main_sequential.cpp:250 */
+  int erode_size;                                /* Erosion::create(3) test_pipeline.cpp:119; 0 = off */
+  int border_mode;                               /* NM03_BORDER_*: sampler addressing of median + sharpen */
+  int sharpen_fma;                               /* 0 = multiply then add, 1 = fused multiply-add */
+  int rg_mode;                                   /* NM03_RG_* */
+  int rg_connectivity;                           /* 4 or 8 */
+  int rg_border_expand;                          /* 1 = image-border pixels expand, 0 = they do not */
+  int se_shape;                                  /* NM03_SE_* */
+  int input_unsigned;                            /* 0 = int16 pixels, 1 = uint16 pixels */
+} nm03_params;
+
+/* Optional per-slice outputs of nm03_process_batch*; any pointer may be NULL.  Each is a dense
+ * [n][h][w] array (host pointers for nm03_process_batch, device pointers for the _device variant). */
+typedef struct nm03_outputs {
+  uint8_t* dilated;    /* final result: dilation->getOutputData<Image>(0)  main_parallel.cpp:161 */
+  uint8_t* eroded;     /* erosion branch off the caster, test_pipeline.cpp:119-121 (needs erode_size>0) */
+  uint8_t* rg_mask;    /* regionGrowing output, {0,1} */
+  float* sharpened;    /* sharpen output (test_pipeline.cpp:71-73) */
+  float* median;       /* medianfilter output */
+  int32_t* rg_iterations; /* [n] passes the flood fill needed to converge */
+} nm03_outputs;
+
+typedef struct nm03_ctx nm03_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+/* Replaces FAST's implicit device manager (first ProcessObject::update()).  gpu_ids: CUDA device
+ * ordinals, one worker (streams + pinned staging + scratch) per entry. */
+int nm03_init(const int* gpu_ids, int n_gpus, nm03_ctx** out);
+void nm03_shutdown(nm03_ctx* ctx);
+const char* nm03_last_error(void);
+int nm03_version(void);
+int nm03_gpu_count(const nm03_ctx* ctx);
+
+/* Literals of main_sequential.cpp:196,200,204,208,233,250 (erosion off, default switches). */
+void nm03_default_params(nm03_params* p);
+
+/* Adaptive dimension-based seeds: main_sequential.cpp:214-241 / main_parallel.cpp:119-148 /
+ * test_pipeline.cpp:79-106.  Writes (x,y) pairs, returns the count (the needed count if cap is
+ * too small), NM03_ERR_TOO_SMALL if w or h < 10 (the reference's loop would not terminate). */
+int nm03_make_seeds(int w, int h, int* xy, int cap);
+
+/* ---- whole pipeline --------------------------------------------------------------------------- */
+/* processSingleImage() for n slices of one size, host buffers in and out (main_parallel.cpp:66-170
+ * applied to a batch, main_parallel.cpp:336-343).  slices: [n][h][w] int16 (or uint16 if
+ * params->input_unsigned).  seeds_xy may be NULL = the adaptive seeds of nm03_make_seeds(w,h).
+ * status (optional, [n]) receives a per-slice nm03_status; a failed slice never poisons the batch
+ * (the reference's catch-and-continue, main_parallel.cpp:163-167). */
+int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
+                       const int* seeds_xy, int n_seeds, const nm03_outputs* out, int* status);
+
+/* Same, but every buffer is already in the memory of GPU `gpu`; work is queued on `stream`
+ * (a cudaStream_t passed as void*, NULL = the worker's own stream) and the call does not wait. */
+int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,
+                              const nm03_params* params, const int* seeds_xy, int n_seeds,
+                              const nm03_outputs* d_out, void* stream);
+
+/* Pinned host memory for zero-copy staging of nm03_process_batch inputs/outputs. */
+int nm03_host_alloc(void** p, size_t bytes);
+int nm03_host_free(void* p);
+
+/* ---- per-operator entry points (host buffers), one per FAST operator on the path ---------------- */
+/* IntensityNormalization + IntensityClipping + VectorMedianFilter + ImageSharpening
+ * (main_sequential.cpp:195-210) as ONE fused kernel.  Outputs optional: median (after median
+ * filter), sharpened, predicate (bit-plane, ceil(w/32) words per row, bit x%32 of word x/32 = 1 iff
+ * rg_min <= sharpened <= rg_max). */
+int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, const nm03_params* params,
+                    float* median, float* sharpened, uint32_t* predicate);
+/* SeededRegionGrowing::create(lo,hi,seeds)->update()  (main_sequential.cpp:232-243). */
+int nm03_region_grow(nm03_ctx* ctx, int gpu, const float* image, int w, int h, const nm03_params* params,
+                     const int* seeds_xy, int n_seeds, uint8_t* mask, int* iterations);
+/* Dilation::create(size) / Erosion::create(size) on a uint8 {0,1} image (main_sequential.cpp:246-252,
+ * test_pipeline.cpp:119-125); ImageCaster(TYPE_UINT8) in front of them is the identity. */
+int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, int size, int se_shape, int op,
+                    uint8_t* out);
+
+/* ---- introspection for benchmarks ------------------------------------------------------------- */
+/* Number of kernel launches this library has issued on `gpu` since nm03_init. */
+long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NM03_H */

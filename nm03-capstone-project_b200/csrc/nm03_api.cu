@@ -1,0 +1,622 @@
+// nm03_api.cu — the extern "C" boundary declared in include/nm03.h.
+//
+// One `Worker` per GPU holds a small pool of stream slots; a slot owns a stream, an event and the
+// scratch bit-plane that carries the range predicate from K1 to K23.  Host threads (the reference
+// runs 16, main_parallel.cpp:401) take a slot, queue copies + two kernels on it and release it;
+// slots make the context re-entrant without any global lock on the data path.
+#include "../../include/nm03.h"
+#include "nm03_device.h"
+
+#include <atomic>
+#include <cmath>
+#include <condition_variable>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) return fail(NM03_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+constexpr int kSlots = 4;
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;     // recorded after the last use of this slot's scratch
+  bool used = false;
+  uint32_t* pred = nullptr;       // scratch: predicate bit-plane [n][h][wpr]
+  size_t pred_bytes = 0;
+  void* stage_in = nullptr;       // scratch: device copy of host inputs
+  size_t stage_in_bytes = 0;
+  void* stage_out = nullptr;      // scratch: device copy of outputs before D2H
+  size_t stage_out_bytes = 0;
+  bool busy = false;
+};
+
+struct Worker {
+  int device = 0;
+  Slot slots[kSlots];
+  std::mutex mu;
+  std::condition_variable cv;
+  std::atomic<long long> launches{0};
+};
+
+}  // namespace
+
+struct nm03_ctx {
+  std::vector<Worker*> workers;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    cudaGetDevice(&cur);
+    if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+Slot* acquire(Worker* wk, bool block = true) {
+  std::unique_lock<std::mutex> lk(wk->mu);
+  for (;;) {
+    for (auto& s : wk->slots)
+      if (!s.busy) { s.busy = true; return &s; }
+    if (!block) return nullptr;
+    wk->cv.wait(lk);
+  }
+}
+
+void release(Worker* wk, Slot* s) {
+  {
+    std::lock_guard<std::mutex> lk(wk->mu);
+    s->busy = false;
+  }
+  wk->cv.notify_one();
+}
+
+struct SlotLease {
+  Worker* wk;
+  Slot* s;
+  explicit SlotLease(Worker* w) : wk(w), s(acquire(w)) {}
+  ~SlotLease() { release(wk, s); }
+};
+
+// grow-only scratch; growing waits for the slot's previous work first
+int ensure(Slot* s, void** buf, size_t* have, size_t need) {
+  if (*have >= need) return NM03_OK;
+  if (s->used) CK(cudaEventSynchronize(s->done));
+  if (*buf) CK(cudaFree(*buf));
+  *buf = nullptr;
+  *have = 0;
+  const size_t want = need + need / 4;
+  cudaError_t e = cudaMalloc(buf, want);
+  if (e != cudaSuccess) return fail(NM03_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+  *have = want;
+  return NM03_OK;
+}
+
+int check_params(const nm03_params* p, int w, int h, bool whole_pipeline) {
+  if (!p) return fail(NM03_ERR_INVALID, "params is null");
+  if (w <= 0 || h <= 0) return fail(NM03_ERR_INVALID, "bad image size %dx%d", w, h);
+  if (whole_pipeline && (w < 100 || h < 100))
+    return fail(NM03_ERR_TOO_SMALL, "Image dimensions too small: %dx%d", w, h);  // main_sequential.cpp:189-192
+  return NM03_OK;
+}
+
+int check_preprocess(const nm03_params* p, int* sharpen_half) {
+  if (p->median_window != 3 && p->median_window != 5 && p->median_window != 7) {
+    if (p->median_window < 1 || (p->median_window & 1) == 0)
+      return fail(NM03_ERR_PARAM, "median window must be odd, got %d", p->median_window);
+    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (3, 5, 7 are)", p->median_window);
+  }
+  int m = p->sharpen_mask;
+  if (m == 0) m = (int)std::ceil(2.0f * p->sharpen_sigma) * 2 + 1;  // FAST's default mask size
+  if (m < 1 || (m & 1) == 0) return fail(NM03_ERR_PARAM, "sharpen mask size must be odd, got %d", m);
+  if (m < 3 || m > 9) return fail(NM03_ERR_UNSUPPORTED, "sharpen mask size %d not implemented (3..9 are)", m);
+  if (!(p->norm_max != p->norm_min)) return fail(NM03_ERR_PARAM, "normalisation range is empty");
+  *sharpen_half = (m - 1) / 2;
+  return NM03_OK;
+}
+
+// host-side twin of the kernel's f(): used only to validate the zero-border sentinel trick
+float f_host(float v, const nm03_params* p) {
+  const float range = p->norm_max - p->norm_min, scale = p->norm_high - p->norm_low;
+  const float t = (v - p->norm_min) / range;
+  const float o = t * scale + p->norm_low;
+  return fminf(fmaxf(o, p->clip_min), p->clip_max);
+}
+
+int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int sharpen_half) {
+  k.w = w; k.h = h; k.n = n; k.wpr = (w + 31) / 32;
+  k.tiles_x = (w + nm03::K1_TW - 1) / nm03::K1_TW;
+  k.tiles_y = (h + nm03::K1_TH - 1) / nm03::K1_TH;
+  k.norm_min = p->norm_min;
+  k.norm_range = p->norm_max - p->norm_min;
+  k.norm_scale = p->norm_high - p->norm_low;
+  k.norm_low = p->norm_low;
+  k.clip_min = p->clip_min; k.clip_max = p->clip_max;
+  k.gain = p->sharpen_gain; k.rg_min = p->rg_min; k.rg_max = p->rg_max;
+  k.border_zero = p->border_mode == NM03_BORDER_ZERO;
+  k.use_fma = p->sharpen_fma != 0;
+  k.input_unsigned = p->input_unsigned != 0;
+  if (k.border_zero) {
+    // outside-image samples are carried as the key -32768; real data is saturated to -32767, which is
+    // only exact if f() does not distinguish the two lowest keys
+    if (k.input_unsigned)
+      return fail(NM03_ERR_UNSUPPORTED, "zero border mode with uint16 input is not implemented");
+    if (f_host(-32768.0f, p) != f_host(-32767.0f, p))
+      return fail(NM03_ERR_UNSUPPORTED, "zero border mode needs f(-32768) == f(-32767) for these parameters");
+  }
+  // normalised Gaussian exactly as FAST's host code builds it: x outer, y inner
+  const int m = 2 * sharpen_half + 1;
+  float sum = 0.0f;
+  for (int x = -sharpen_half; x <= sharpen_half; ++x)
+    for (int y = -sharpen_half; y <= sharpen_half; ++y) {
+      const float v = expf(-(float)(x * x + y * y) / (2.0f * p->sharpen_sigma * p->sharpen_sigma));
+      k.mask[x + sharpen_half + (y + sharpen_half) * m] = v;
+      sum += v;
+    }
+  for (int i = 0; i < m * m; ++i) k.mask[i] /= sum;
+  for (int i = m * m; i < 81; ++i) k.mask[i] = 0.0f;
+  return NM03_OK;
+}
+
+int se_halfwidths(int size, int se_shape, int* n_out, int8_t* hw) {
+  if (size <= 2 || (size & 1) == 0)
+    return fail(NM03_ERR_PARAM, "morphology size must be odd and > 2, got %d", size);  // FAST throws
+  const int N = size / 2;
+  if (N > nm03::SEG_HALO) return fail(NM03_ERR_UNSUPPORTED, "morphology size %d not implemented (<= 15 is)", size);
+  for (int b = -N; b <= N; ++b) {
+    int a = N;
+    if (se_shape != NM03_SE_SQUARE)
+      while (a * a + b * b > N * N) --a;  // disc: offsets with a*a + b*b <= N*N
+    hw[b + N] = (int8_t)a;
+  }
+  *n_out = N;
+  return NM03_OK;
+}
+
+// cluster size: the smallest power of two whose per-CTA planes fit in shared memory, widened while
+// the batch alone cannot fill the 148 SMs
+int pick_cluster(int n, int h, int wpr, int* rows_per) {
+  const size_t cap = 200 * 1024;
+  int c = 1;
+  for (;; c *= 2) {
+    const int rows = (h + c - 1) / c;
+    if (nm03::seg_smem_bytes(rows, wpr) <= cap) break;
+    if (c == nm03::SEG_MAX_CLUSTER) return fail(NM03_ERR_TOO_LARGE, "slice of %d rows x %d words exceeds cluster capacity", h, wpr);
+  }
+  while (c < nm03::SEG_MAX_CLUSTER && n * c * 2 <= 148 && (h + 2 * c - 1) / (2 * c) >= 32) c *= 2;
+  *rows_per = (h + c - 1) / c;
+  return c;
+}
+
+int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, const int* seeds_xy, int n_seeds,
+             bool do_fill) {
+  memset(&k, 0, sizeof(k));
+  k.w = w; k.h = h; k.n = n; k.wpr = (w + 31) / 32;
+  int rows = 0;
+  const int c = pick_cluster(n, h, k.wpr, &rows);
+  if (c < 0) return c;
+  k.cluster = c;
+  k.rows_per = rows;
+  int seg = (rows * k.wpr + nm03::SEG_THREADS - 1) / nm03::SEG_THREADS;
+  k.seg_rows = seg < 4 ? 4 : seg;
+  k.do_fill = do_fill;
+  if (do_fill) {
+    if (p->rg_connectivity != 4 && p->rg_connectivity != 8)
+      return fail(NM03_ERR_PARAM, "region growing connectivity must be 4 or 8, got %d", p->rg_connectivity);
+    k.conn8 = p->rg_connectivity == 8;
+    k.border_expand = p->rg_border_expand != 0;
+    k.host_mode = p->rg_mode == NM03_RG_HOST;
+    int auto_seeds[2 * nm03::SEG_MAX_SEEDS];
+    if (!seeds_xy) {
+      n_seeds = nm03_make_seeds(w, h, auto_seeds, nm03::SEG_MAX_SEEDS);
+      if (n_seeds < 0) return n_seeds;
+      seeds_xy = auto_seeds;
+    }
+    if (n_seeds <= 0) return fail(NM03_ERR_NO_SEEDS, "no seed points");              // FAST throws
+    if (n_seeds > nm03::SEG_MAX_SEEDS)
+      return fail(NM03_ERR_UNSUPPORTED, "%d seed points (at most %d are supported)", n_seeds, nm03::SEG_MAX_SEEDS);
+    for (int i = 0; i < n_seeds; ++i) {
+      const int x = seeds_xy[2 * i], y = seeds_xy[2 * i + 1];
+      if (x < 0 || y < 0 || x >= w || y >= h)
+        return fail(NM03_ERR_SEED_OOB, "seed point (%d,%d) outside %dx%d image", x, y, w, h);  // FAST throws
+      k.seeds[i].x = (short)x;
+      k.seeds[i].y = (short)y;
+    }
+    k.n_seeds = n_seeds;
+  }
+  return NM03_OK;
+}
+
+int get_worker(nm03_ctx* ctx, int gpu, Worker** wk) {
+  if (!ctx) return fail(NM03_ERR_INVALID, "context is null");
+  if (gpu < 0 || gpu >= (int)ctx->workers.size())
+    return fail(NM03_ERR_INVALID, "gpu index %d out of range (context has %zu)", gpu, ctx->workers.size());
+  *wk = ctx->workers[gpu];
+  return NM03_OK;
+}
+
+// queue K1 + K23 for n device-resident slices on `st`
+int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h,
+                     const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out) {
+  int rc, hs = 0;
+  if ((rc = check_params(p, w, h, true))) return rc;
+  if ((rc = check_preprocess(p, &hs))) return rc;
+  nm03::PreParams pre;
+  if ((rc = fill_pre(pre, p, n, w, h, hs))) return rc;
+  nm03::SegParams seg;
+  if ((rc = fill_seg(seg, p, n, w, h, seeds_xy, n_seeds, true))) return rc;
+  if ((rc = se_halfwidths(p->dilate_size, p->se_shape, &seg.dil_n, seg.dil_hw))) return rc;
+  if (p->erode_size > 0 && d_out->eroded) {
+    if ((rc = se_halfwidths(p->erode_size, p->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
+  }
+  const size_t pred_bytes = (size_t)n * h * pre.wpr * 4;
+  if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pred_bytes))) return rc;
+  if (s->used && st != s->stream) CK(cudaStreamWaitEvent(st, s->done, 0));  // scratch reuse across streams
+  pre.in = d_slices;
+  pre.median = d_out->median;
+  pre.sharpened = d_out->sharpened;
+  pre.predicate = s->pred;
+  CK(nm03::launch_preprocess(pre, p->median_window, hs, st));
+  seg.pred = s->pred;
+  seg.dilated = d_out->dilated;
+  seg.eroded = (p->erode_size > 0) ? d_out->eroded : nullptr;
+  seg.rg_mask = d_out->rg_mask;
+  seg.iterations = d_out->rg_iterations;
+  CK(nm03::launch_segment(seg, st));
+  wk->launches += 2;
+  CK(cudaEventRecord(s->done, st));
+  s->used = true;
+  return NM03_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* nm03_last_error(void) { return g_err; }
+int nm03_version(void) { return 100; }
+
+void nm03_default_params(nm03_params* p) {
+  if (!p) return;
+  p->norm_low = 0.5f; p->norm_high = 2.5f; p->norm_min = 0.0f; p->norm_max = 10000.0f;  // main_sequential.cpp:196
+  p->clip_min = 0.68f; p->clip_max = 4000.0f;                                           // :200
+  p->median_window = 7;                                                                 // :204
+  p->sharpen_gain = 2.0f; p->sharpen_sigma = 0.5f; p->sharpen_mask = 9;                 // :208
+  p->rg_min = 0.74f; p->rg_max = 0.91f;                                                 // :233
+  p->dilate_size = 3;                                                                   // :250
+  p->erode_size = 0;
+  p->border_mode = NM03_BORDER_CLAMP;
+  p->sharpen_fma = 0;
+  p->rg_mode = NM03_RG_OPENCL;
+  p->rg_connectivity = 4;
+  p->rg_border_expand = 1;
+  p->se_shape = NM03_SE_DISC;
+  p->input_unsigned = 0;
+}
+
+int nm03_make_seeds(int w, int h, int* xy, int cap) {
+  if (w < 10 || h < 10) return fail(NM03_ERR_TOO_SMALL, "image %dx%d too small for the seed grid", w, h);
+  int n = 0;
+  auto put = [&](int x, int y) {
+    if (xy && n < cap) { xy[2 * n] = x; xy[2 * n + 1] = y; }
+    ++n;
+  };
+  const int cx = w / 2, cy = h / 2, ox = w / 8, oy = h / 8;  // main_sequential.cpp:214-230
+  put(cx, cy);
+  put(cx + ox, cy);
+  put(cx - ox, cy);
+  put(cx, cy + oy);
+  put(cx, cy - oy);
+  for (int x = w / 4; x < w * 3 / 4; x += w / 10)            // main_sequential.cpp:237-241
+    for (int y = h / 4; y < h * 3 / 4; y += h / 10) put(x, y);
+  return n;
+}
+
+int nm03_init(const int* gpu_ids, int n_gpus, nm03_ctx** out) {
+  if (!out) return fail(NM03_ERR_INVALID, "out is null");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(NM03_ERR_NO_DEVICE, "no CUDA device (%s); this library has no CPU fallback",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+  int def = 0;
+  if (!gpu_ids || n_gpus <= 0) { gpu_ids = &def; n_gpus = 1; cudaGetDevice(&def); }
+  nm03_ctx* ctx = new nm03_ctx();
+  for (int i = 0; i < n_gpus; ++i) {
+    if (gpu_ids[i] < 0 || gpu_ids[i] >= count) {
+      nm03_shutdown(ctx);
+      return fail(NM03_ERR_INVALID, "device ordinal %d out of range (%d devices)", gpu_ids[i], count);
+    }
+    Worker* wk = new Worker();
+    wk->device = gpu_ids[i];
+    ctx->workers.push_back(wk);
+    DeviceGuard g(wk->device);
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, wk->device);
+    if (e == cudaSuccess && prop.major < 10) {
+      nm03_shutdown(ctx);
+      return fail(NM03_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", wk->device,
+                  prop.major, prop.minor);
+    }
+    if (e == cudaSuccess) e = nm03::configure_kernels();
+    for (auto& s : wk->slots) {
+      if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) {
+      nm03_shutdown(ctx);
+      return fail(NM03_ERR_CUDA, "device %d setup failed: %s", gpu_ids[i], cudaGetErrorString(e));
+    }
+  }
+  *out = ctx;
+  return NM03_OK;
+}
+
+void nm03_shutdown(nm03_ctx* ctx) {
+  if (!ctx) return;
+  for (Worker* wk : ctx->workers) {
+    DeviceGuard g(wk->device);
+    for (auto& s : wk->slots) {
+      if (s.stream) cudaStreamSynchronize(s.stream);
+      if (s.pred) cudaFree(s.pred);
+      if (s.stage_in) cudaFree(s.stage_in);
+      if (s.stage_out) cudaFree(s.stage_out);
+      if (s.done) cudaEventDestroy(s.done);
+      if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    delete wk;
+  }
+  delete ctx;
+}
+
+int nm03_gpu_count(const nm03_ctx* ctx) { return ctx ? (int)ctx->workers.size() : 0; }
+
+long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu) {
+  if (!ctx || gpu < 0 || gpu >= (int)ctx->workers.size()) return -1;
+  return ctx->workers[gpu]->launches.load();
+}
+
+int nm03_host_alloc(void** p, size_t bytes) {
+  if (!p) return fail(NM03_ERR_INVALID, "p is null");
+  cudaError_t e = cudaHostAlloc(p, bytes, cudaHostAllocPortable);
+  if (e != cudaSuccess) return fail(NM03_ERR_NOMEM, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+  return NM03_OK;
+}
+
+int nm03_host_free(void* p) {
+  if (!p) return NM03_OK;
+  CK(cudaFreeHost(p));
+  return NM03_OK;
+}
+
+int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,
+                              const nm03_params* params, const int* seeds_xy, int n_seeds,
+                              const nm03_outputs* d_out, void* stream) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!d_slices || !d_out || n < 0) return fail(NM03_ERR_INVALID, "null buffer or negative count");
+  if (n == 0) return NM03_OK;
+  DeviceGuard g(wk->device);
+  SlotLease lease(wk);
+  cudaStream_t st = stream ? (cudaStream_t)stream : lease.s->stream;
+  return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out);
+}
+
+int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
+                       const int* seeds_xy, int n_seeds, const nm03_outputs* out, int* status) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!slices || !out || n < 0) return fail(NM03_ERR_INVALID, "null buffer or negative count");
+  if (n == 0) return NM03_OK;
+  if ((rc = check_params(params, w, h, true))) {
+    if (status) for (int i = 0; i < n; ++i) status[i] = rc;
+    return rc;
+  }
+  DeviceGuard g(wk->device);
+  const size_t npx = (size_t)w * h;
+  // Chunks of the batch are pipelined over the stream slots so that the H2D copy of one chunk, the
+  // kernels of another and the D2H copy of a third overlap.
+  int chunk = (n + kSlots - 1) / kSlots;
+  if (chunk < 4) chunk = 4;
+  std::vector<Slot*> used;
+  int result = NM03_OK;
+  for (int start = 0; start < n; start += chunk) {
+    const int cnt = (n - start < chunk) ? n - start : chunk;
+    // never wait for a slot while holding one (two batches could starve each other): when none is
+    // free, drain and reuse the oldest slot of this call instead
+    Slot* s = acquire(wk, used.empty());
+    if (!s) {
+      s = used.front();
+      used.erase(used.begin());
+      cudaStreamSynchronize(s->stream);
+    }
+    used.push_back(s);
+    // per-chunk device staging laid out as [inputs][dilated][eroded][rg_mask][sharpened][median][iters]
+    size_t out_bytes = 0;
+    const size_t o_dil = out_bytes; if (out->dilated) out_bytes += cnt * npx;
+    const size_t o_ero = out_bytes; if (out->eroded) out_bytes += cnt * npx;
+    const size_t o_rg = out_bytes; if (out->rg_mask) out_bytes += cnt * npx;
+    out_bytes = (out_bytes + 15) & ~(size_t)15;
+    const size_t o_sh = out_bytes; if (out->sharpened) out_bytes += cnt * npx * 4;
+    const size_t o_med = out_bytes; if (out->median) out_bytes += cnt * npx * 4;
+    const size_t o_it = out_bytes; if (out->rg_iterations) out_bytes += (size_t)cnt * 4;
+    rc = ensure(s, &s->stage_in, &s->stage_in_bytes, cnt * npx * 2);
+    if (!rc) rc = ensure(s, &s->stage_out, &s->stage_out_bytes, out_bytes ? out_bytes : 16);
+    if (rc) { result = rc; break; }
+    cudaStream_t st = s->stream;
+    cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
+                                    cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e)); break; }
+    uint8_t* so = (uint8_t*)s->stage_out;
+    nm03_outputs d = {};
+    if (out->dilated) d.dilated = so + o_dil;
+    if (out->eroded) d.eroded = so + o_ero;
+    if (out->rg_mask) d.rg_mask = so + o_rg;
+    if (out->sharpened) d.sharpened = (float*)(so + o_sh);
+    if (out->median) d.median = (float*)(so + o_med);
+    if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
+    rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d);
+    if (rc) { result = rc; break; }
+#define NM03_D2H(field, off, elem)                                                                          \
+  if (out->field && e == cudaSuccess)                                                                       \
+    e = cudaMemcpyAsync((uint8_t*)out->field + (size_t)start * npx * (elem), so + (off), cnt * npx * (elem), \
+                        cudaMemcpyDeviceToHost, st);
+    NM03_D2H(dilated, o_dil, 1)
+    NM03_D2H(eroded, o_ero, 1)
+    NM03_D2H(rg_mask, o_rg, 1)
+    NM03_D2H(sharpened, o_sh, 4)
+    NM03_D2H(median, o_med, 4)
+#undef NM03_D2H
+    if (out->rg_iterations && e == cudaSuccess)
+      e = cudaMemcpyAsync(out->rg_iterations + start, so + o_it, (size_t)cnt * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
+    if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e)); break; }
+    // keep at most kSlots chunks in flight: the oldest slot is drained and handed back
+    if ((int)used.size() == kSlots) {
+      Slot* old = used.front();
+      used.erase(used.begin());
+      cudaStreamSynchronize(old->stream);
+      release(wk, old);
+    }
+  }
+  for (Slot* s : used) {
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    if (e != cudaSuccess && result == NM03_OK) result = fail(NM03_ERR_CUDA, "pipeline failed: %s", cudaGetErrorString(e));
+    release(wk, s);
+  }
+  if (status) for (int i = 0; i < n; ++i) status[i] = result;
+  return result;
+}
+
+int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, const nm03_params* params,
+                    float* median, float* sharpened, uint32_t* predicate) {
+  Worker* wk;
+  int rc, hs = 0;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!slice) return fail(NM03_ERR_INVALID, "slice is null");
+  if ((rc = check_params(params, w, h, false))) return rc;
+  if ((rc = check_preprocess(params, &hs))) return rc;
+  nm03::PreParams pre;
+  if ((rc = fill_pre(pre, params, 1, w, h, hs))) return rc;
+  DeviceGuard g(wk->device);
+  SlotLease lease(wk);
+  Slot* s = lease.s;
+  const size_t npx = (size_t)w * h, pw = (size_t)h * pre.wpr * 4;
+  if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx * 2))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx * 8 + pw + 16))) return rc;
+  uint8_t* so = (uint8_t*)s->stage_out;
+  CK(cudaMemcpyAsync(s->stage_in, slice, npx * 2, cudaMemcpyHostToDevice, s->stream));
+  pre.in = s->stage_in;
+  pre.median = median ? (float*)so : nullptr;
+  pre.sharpened = sharpened ? (float*)(so + npx * 4) : nullptr;
+  pre.predicate = predicate ? (uint32_t*)(so + npx * 8) : nullptr;
+  CK(nm03::launch_preprocess(pre, params->median_window, hs, s->stream));
+  wk->launches += 1;
+  if (median) CK(cudaMemcpyAsync(median, pre.median, npx * 4, cudaMemcpyDeviceToHost, s->stream));
+  if (sharpened) CK(cudaMemcpyAsync(sharpened, pre.sharpened, npx * 4, cudaMemcpyDeviceToHost, s->stream));
+  if (predicate) CK(cudaMemcpyAsync(predicate, pre.predicate, pw, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaEventRecord(s->done, s->stream));
+  s->used = true;
+  CK(cudaStreamSynchronize(s->stream));
+  return NM03_OK;
+}
+
+int nm03_region_grow(nm03_ctx* ctx, int gpu, const float* image, int w, int h, const nm03_params* params,
+                     const int* seeds_xy, int n_seeds, uint8_t* mask, int* iterations) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!image || !mask) return fail(NM03_ERR_INVALID, "null buffer");
+  if ((rc = check_params(params, w, h, false))) return rc;
+  if (!seeds_xy || n_seeds <= 0) return fail(NM03_ERR_NO_SEEDS, "no seed points");
+  nm03::SegParams seg;
+  if ((rc = fill_seg(seg, params, 1, w, h, seeds_xy, n_seeds, true))) return rc;
+  DeviceGuard g(wk->device);
+  SlotLease lease(wk);
+  Slot* s = lease.s;
+  const size_t npx = (size_t)w * h, pw = (size_t)h * seg.wpr * 4;
+  if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx * 4))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx + 16))) return rc;
+  if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pw))) return rc;
+  CK(cudaMemcpyAsync(s->stage_in, image, npx * 4, cudaMemcpyHostToDevice, s->stream));
+  CK(nm03::launch_threshold_pack((const float*)s->stage_in, 1, w, h, params->rg_min, params->rg_max, s->pred, s->stream));
+  seg.pred = s->pred;
+  seg.rg_mask = (uint8_t*)s->stage_out;
+  seg.iterations = (int32_t*)((uint8_t*)s->stage_out + ((npx + 3) & ~(size_t)3));
+  CK(nm03::launch_segment(seg, s->stream));
+  wk->launches += 2;
+  CK(cudaMemcpyAsync(mask, seg.rg_mask, npx, cudaMemcpyDeviceToHost, s->stream));
+  int it = 0;
+  CK(cudaMemcpyAsync(&it, seg.iterations, 4, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaEventRecord(s->done, s->stream));
+  s->used = true;
+  CK(cudaStreamSynchronize(s->stream));
+  if (iterations) *iterations = it;
+  return NM03_OK;
+}
+
+int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, int size, int se_shape, int op,
+                    uint8_t* out) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!mask || !out) return fail(NM03_ERR_INVALID, "null buffer");
+  if (w <= 0 || h <= 0) return fail(NM03_ERR_INVALID, "bad image size %dx%d", w, h);
+  if (op != NM03_MORPH_DILATE && op != NM03_MORPH_ERODE) return fail(NM03_ERR_INVALID, "bad morphology op %d", op);
+  nm03_params dummy;
+  nm03_default_params(&dummy);
+  nm03::SegParams seg;
+  if ((rc = fill_seg(seg, &dummy, 1, w, h, nullptr, 0, false))) return rc;
+  if (op == NM03_MORPH_DILATE) rc = se_halfwidths(size, se_shape, &seg.dil_n, seg.dil_hw);
+  else rc = se_halfwidths(size, se_shape, &seg.ero_n, seg.ero_hw);
+  if (rc) return rc;
+  DeviceGuard g(wk->device);
+  SlotLease lease(wk);
+  Slot* s = lease.s;
+  const size_t npx = (size_t)w * h, pw = (size_t)h * seg.wpr * 4;
+  if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx))) return rc;
+  if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pw))) return rc;
+  CK(cudaMemcpyAsync(s->stage_in, mask, npx, cudaMemcpyHostToDevice, s->stream));
+  CK(nm03::launch_pack_u8((const uint8_t*)s->stage_in, 1, w, h, s->pred, s->stream));
+  seg.pred = s->pred;
+  if (op == NM03_MORPH_DILATE) seg.dilated = (uint8_t*)s->stage_out;
+  else seg.eroded = (uint8_t*)s->stage_out;
+  CK(nm03::launch_segment(seg, s->stream));
+  wk->launches += 2;
+  CK(cudaMemcpyAsync(out, s->stage_out, npx, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaEventRecord(s->done, s->stream));
+  s->used = true;
+  CK(cudaStreamSynchronize(s->stream));
+  return NM03_OK;
+}
+
+}  // extern "C"

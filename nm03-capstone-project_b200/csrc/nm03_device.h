@@ -1,0 +1,69 @@
+// nm03_device.h — parameter blocks shared by the kernels (nm03_kernels.cu) and the C-ABI host
+// code (nm03_api.cu).  Everything is passed to the kernels by value (kernel parameter space).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nm03 {
+
+// ---- K1: fused normalise + clip + median + sharpen + range predicate --------------------------
+// Output tile of one CTA.  The median is needed on the tile plus the sharpen halo (HS_MAX each
+// side); raw samples on that plus the median radius.
+constexpr int K1_TW = 128;
+constexpr int K1_TH = 64;
+constexpr int K1_HS_MAX = 4;                      // sharpen mask up to 9x9
+constexpr int K1_MW = K1_TW + 2 * K1_HS_MAX;      // 136 median columns
+constexpr int K1_MH = K1_TH + 2 * K1_HS_MAX;      // 72 median rows
+constexpr int K1_MHP = K1_MH / 2;                 // 36 packed median rows (row p and row p+36 share a register)
+constexpr int K1_PWS = 144;                       // packed raw tile row stride in words (>= 136 + 6, multiple of 4)
+constexpr int K1_THREADS = 256;
+
+struct PreParams {
+  const void* in;        // [n][h][w] int16 / uint16
+  float* median;         // optional [n][h][w]
+  float* sharpened;      // optional [n][h][w]
+  uint32_t* predicate;   // optional [n][h][wpr] bit-plane
+  int w, h, n, wpr;
+  int tiles_x, tiles_y;
+  float norm_min, norm_range, norm_scale, norm_low;  // t=(v-min)/range ; t*scale+low
+  float clip_min, clip_max;
+  float gain, rg_min, rg_max;
+  int border_zero, use_fma, input_unsigned;
+  float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
+};
+
+// ---- K2+K3: flood fill + morphology on bit-packed planes, one thread-block cluster per slice ----
+constexpr int SEG_THREADS = 256;
+constexpr int SEG_HALO = 7;            // rows of the neighbouring CTA's mask kept for the SE (size <= 15)
+constexpr int SEG_MAX_SEEDS = 512;
+constexpr int SEG_MAX_CLUSTER = 8;
+
+struct SegParams {
+  const uint32_t* pred;  // [n][h][wpr]: range predicate (do_fill=1) or the mask itself (do_fill=0)
+  uint8_t* dilated;      // optional [n][h][w]
+  uint8_t* eroded;       // optional
+  uint8_t* rg_mask;      // optional
+  int32_t* iterations;   // optional [n]
+  int w, h, n, wpr;
+  int cluster;           // CTAs per slice
+  int rows_per;          // rows owned by one CTA
+  int seg_rows;          // rows swept by one thread per pass
+  int do_fill, conn8, border_expand, host_mode;
+  int dil_n, ero_n;      // SE radius N = size/2 (0 = stage off)
+  int8_t dil_hw[16];     // horizontal half-width of the SE at row offset b (index b + N)
+  int8_t ero_hw[16];
+  int n_seeds;
+  short2 seeds[SEG_MAX_SEEDS];
+};
+
+size_t seg_smem_bytes(int rows_per, int wpr);
+
+// launchers (return cudaError_t of the launch)
+cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, cudaStream_t s);
+cudaError_t launch_segment(const SegParams& p, cudaStream_t s);
+cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float lo, float hi, uint32_t* bits,
+                                  cudaStream_t s);
+cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* bits, cudaStream_t s);
+cudaError_t configure_kernels();  // opt in to large dynamic shared memory; once per device
+
+}  // namespace nm03

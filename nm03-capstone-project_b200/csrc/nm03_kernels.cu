@@ -1,0 +1,579 @@
+// nm03_kernels.cu — sm_100a kernels of the per-slice brain-MRI pipeline.
+//
+//   K1  k1_preprocess   IntensityNormalization + IntensityClipping + VectorMedianFilter +
+//                       ImageSharpening (+ the region-growing range test) in one pass over the raw
+//                       int16 slice  (reference main_sequential.cpp:195-210, :233).
+//   K23 k23_segment     SeededRegionGrowing + ImageCaster + Dilation/Erosion on bit-packed planes
+//                       held in (distributed) shared memory, one thread-block cluster per slice
+//                       (reference main_sequential.cpp:232-252, test_pipeline.cpp:119-125).
+//
+// Nothing here is a dense contraction, so no tensor cores: K1 is bound by the integer min/max
+// pipe (packed VIMNMX.S16x2 networks), K23 by shared-memory latency.  Built with -fmad=false; the
+// places where rounding must follow the oracle use explicit _rn intrinsics.
+#include "nm03_device.h"
+
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+
+namespace cg = cooperative_groups;
+
+#define NM03_MIN(a, b) __vmins2((a), (b))
+#define NM03_MAX(a, b) __vmaxs2((a), (b))
+#define NM03_MIN3(a, b, c) __vimin3_s16x2((a), (b), (c))
+#define NM03_MAX3(a, b, c) __vimax3_s16x2((a), (b), (c))
+#include "median_net.inc"
+
+namespace nm03 {
+
+// =================================================================================================
+// K1
+// =================================================================================================
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+// Raw sample as an order-preserving signed 16-bit key.  uint16 input is biased by 0x8000.  In
+// zero-border mode samples outside the image become the sentinel -32768 (maps to 0.0f later) and
+// real data is saturated at -32767 (the host has checked that this does not change f()).
+template <bool ZERO>
+__device__ __forceinline__ uint32_t fetch_key(const uint16_t* __restrict__ img, int w, int h, int x, int y,
+                                              uint32_t bias) {
+  if (ZERO) {
+    if (x < 0 || y < 0 || x >= w || y >= h) return 0x8000u;
+    uint32_t v = (img[(size_t)y * w + x] ^ bias) & 0xffffu;
+    return v == 0x8000u ? 0x8001u : v;
+  }
+  return (img[(size_t)clampi(y, 0, h - 1) * w + clampi(x, 0, w - 1)] ^ bias) & 0xffffu;
+}
+
+// f(key) = clip(normalise(raw))  — oracle nm03o_normalize / nm03o_clip, same operation order.
+__device__ __forceinline__ float key_to_float(int key, const PreParams& p) {
+  if (p.border_zero && key == -32768) return 0.0f;
+  const float v = p.input_unsigned ? (float)((key ^ 0x8000) & 0xffff) : (float)key;
+  const float t = __fdiv_rn(__fsub_rn(v, p.norm_min), p.norm_range);
+  const float o = __fadd_rn(__fmul_rn(t, p.norm_scale), p.norm_low);
+  return fminf(fmaxf(o, p.clip_min), p.clip_max);
+}
+
+template <int K>
+struct MedianRun;
+template <>
+struct MedianRun<3> {
+  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 2][3], uint32_t (&o)[NM03_MEDIAN_RUN]) {
+    NM03_MEDIAN_RUN_3(v, o);
+  }
+};
+template <>
+struct MedianRun<5> {
+  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 4][5], uint32_t (&o)[NM03_MEDIAN_RUN]) {
+    NM03_MEDIAN_RUN_5(v, o);
+  }
+};
+template <>
+struct MedianRun<7> {
+  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 6][7], uint32_t (&o)[NM03_MEDIAN_RUN]) {
+    NM03_MEDIAN_RUN_7(v, o);
+  }
+};
+
+// Unsharp mask for 4 horizontally adjacent pixels, accumulating exactly in the oracle's order
+// (tap x outer, tap y inner, from 0.0f; nm03o_sharpen).  M points at the median tile row of the
+// pixels' centre minus HS rows, column 4*xq of the 12-column frame.
+template <int HS, bool FMA>
+__device__ __forceinline__ void blur4(const float* __restrict__ Mrow0, int mws, const PreParams& p, float (&acc)[4]) {
+  constexpr int m = 2 * HS + 1;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc[j] = 0.0f;
+#pragma unroll
+  for (int cgp = 0; cgp < 3; ++cgp) {
+    float4 t[m];
+#pragma unroll
+    for (int yi = 0; yi < m; ++yi) t[yi] = *reinterpret_cast<const float4*>(Mrow0 + yi * mws + 4 * cgp);
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      const int c = 4 * cgp + cc;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int xi = c - j - (K1_HS_MAX - HS);
+        if (xi < 0 || xi >= m) continue;
+#pragma unroll
+        for (int yi = 0; yi < m; ++yi) {
+          const float v = cc == 0 ? t[yi].x : cc == 1 ? t[yi].y : cc == 2 ? t[yi].z : t[yi].w;
+          const float wgt = p.mask[xi + yi * m];
+          if (FMA) acc[j] = __fmaf_rn(wgt, v, acc[j]);
+          else acc[j] = __fadd_rn(acc[j], __fmul_rn(wgt, v));
+        }
+      }
+    }
+  }
+}
+
+template <int K, int HS>
+__global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_constant__ PreParams p) {
+  constexpr int R = K / 2;
+  constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
+  constexpr int RW = K1_MW + 2 * R;        // raw columns actually needed
+  constexpr int NRUN = K1_MW / NM03_MEDIAN_RUN;
+  static_assert(RW <= K1_PWS, "packed tile stride too small");
+  static_assert(K1_MW % NM03_MEDIAN_RUN == 0, "median tile width must be a multiple of the run length");
+
+  extern __shared__ __align__(16) uint32_t smem[];
+  uint32_t* P = smem;                                         // [PR][K1_PWS] packed keys (row q | row q+36 <<16)
+  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median)
+
+  const int tid = threadIdx.x;
+  int tile = blockIdx.x;
+  const int tx = tile % p.tiles_x;
+  tile /= p.tiles_x;
+  const int ty = tile % p.tiles_y;
+  const int slice = tile / p.tiles_y;
+  const int x0 = tx * K1_TW, y0 = ty * K1_TH;
+  const int w = p.w, h = p.h;
+  const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
+  const uint32_t bias = p.input_unsigned ? 0x8000u : 0u;
+
+  // ---- phase A: raw halo tile -> packed keys --------------------------------------------------
+  {
+    const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
+    for (int idx = tid; idx < PR * K1_PWS; idx += K1_THREADS) {
+      const int q = idx / K1_PWS, col = idx - q * K1_PWS;
+      uint32_t a, b;
+      if (p.border_zero) {
+        a = fetch_key<true>(img, w, h, gx0 + col, gy0 + q, bias);
+        b = fetch_key<true>(img, w, h, gx0 + col, gy0 + q + K1_MHP, bias);
+      } else {
+        a = fetch_key<false>(img, w, h, gx0 + col, gy0 + q, bias);
+        b = fetch_key<false>(img, w, h, gx0 + col, gy0 + q + K1_MHP, bias);
+      }
+      P[idx] = a | (b << 16);
+    }
+  }
+  __syncthreads();
+
+  // ---- phase B: median of the K x K window on packed keys, then f() ---------------------------
+  for (int it = tid; it < K1_MHP * NRUN; it += K1_THREADS) {
+    const int prow = it / NRUN, run = it - prow * NRUN;
+    uint32_t v[NM03_MEDIAN_RUN + K - 1][K], o[NM03_MEDIAN_RUN];
+    const uint32_t* src = P + prow * K1_PWS + run * NM03_MEDIAN_RUN;
+#pragma unroll
+    for (int r = 0; r < K; ++r)
+#pragma unroll
+      for (int c = 0; c < NM03_MEDIAN_RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
+    MedianRun<K>::run(v, o);
+    float lo[NM03_MEDIAN_RUN], hi[NM03_MEDIAN_RUN];
+#pragma unroll
+    for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
+      lo[i] = key_to_float((int)(short)(o[i] & 0xffffu), p);
+      hi[i] = key_to_float((int)(short)(o[i] >> 16), p);
+    }
+    float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
+    float* mhi = mlo + K1_MHP * K1_MW;
+    *reinterpret_cast<float4*>(mlo) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<float4*>(mhi) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+  }
+  __syncthreads();
+
+  // ---- phase B': the sharpen stage samples the MEDIAN IMAGE with clamp-to-edge (or zero), so
+  // median-tile entries whose coordinates fall outside the image are replaced (not recomputed from
+  // replicated raw samples).
+  const int mx0 = x0 - K1_HS_MAX, my0 = y0 - K1_HS_MAX;
+  if (mx0 < 0 || my0 < 0 || mx0 + K1_MW > w || my0 + K1_MH > h) {
+    for (int idx = tid; idx < K1_MH * K1_MW; idx += K1_THREADS) {
+      const int my = idx / K1_MW, mx = idx - my * K1_MW;
+      const int gx = mx0 + mx, gy = my0 + my;
+      if (gx < 0 || gy < 0 || gx >= w || gy >= h) {
+        float val = 0.0f;
+        if (!p.border_zero) {
+          const int cx = clampi(gx, 0, w - 1) - mx0, cy = clampi(gy, 0, h - 1) - my0;
+          // tiles that start beyond the image never reach here with a valid centre; guard anyway
+          val = (cx >= 0 && cy >= 0 && cx < K1_MW && cy < K1_MH) ? M[cy * K1_MW + cx] : 0.0f;
+        }
+        M[idx] = val;
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- phase C: unsharp mask, range predicate, stores (one warp = one 128-pixel output row) ----
+  const int lane = tid & 31;
+  for (int it = tid; it < K1_TH * (K1_TW / 4); it += K1_THREADS) {
+    const int oyl = it / (K1_TW / 4), xq = it - oyl * (K1_TW / 4);
+    const int oy = y0 + oyl, ox = x0 + 4 * xq;
+    if (oy >= h) continue;  // warp-uniform: a warp owns one row
+    const float* mrow0 = M + (oyl + K1_HS_MAX - HS) * K1_MW + 4 * xq;
+    float blur[4];
+    if (p.use_fma) blur4<HS, true>(mrow0, K1_MW, p, blur);
+    else blur4<HS, false>(mrow0, K1_MW, p, blur);
+    const float4 c4 = *reinterpret_cast<const float4*>(M + (oyl + K1_HS_MAX) * K1_MW + 4 * xq + K1_HS_MAX);
+    const float cv[4] = {c4.x, c4.y, c4.z, c4.w};
+    float sv[4];
+    uint32_t nib = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float d = __fsub_rn(cv[j], blur[j]);
+      sv[j] = __fadd_rn(cv[j], __fmul_rn(p.gain, d));
+      if (ox + j < w && sv[j] >= p.rg_min && sv[j] <= p.rg_max) nib |= 1u << j;
+    }
+    const size_t rowoff = ((size_t)slice * h + oy) * w;
+    if (p.sharpened) {
+      if ((w & 3) == 0 && ox + 3 < w) *reinterpret_cast<float4*>(p.sharpened + rowoff + ox) = make_float4(sv[0], sv[1], sv[2], sv[3]);
+      else
+#pragma unroll
+        for (int j = 0; j < 4; ++j) if (ox + j < w) p.sharpened[rowoff + ox + j] = sv[j];
+    }
+    if (p.median) {
+      if ((w & 3) == 0 && ox + 3 < w) *reinterpret_cast<float4*>(p.median + rowoff + ox) = c4;
+      else
+#pragma unroll
+        for (int j = 0; j < 4; ++j) if (ox + j < w) p.median[rowoff + ox + j] = cv[j];
+    }
+    // 8 lanes x 4 bits -> one 32-pixel word of the predicate bit-plane
+    uint32_t word = nib << (4 * (lane & 7));
+    word |= __shfl_xor_sync(0xffffffffu, word, 1);
+    word |= __shfl_xor_sync(0xffffffffu, word, 2);
+    word |= __shfl_xor_sync(0xffffffffu, word, 4);
+    if (p.predicate && (lane & 7) == 0) {
+      const int wi = (x0 >> 5) + (lane >> 3);
+      if (wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = word;
+    }
+  }
+}
+
+template <int K, int HS>
+static cudaError_t launch_k1(const PreParams& p, cudaStream_t s) {
+  constexpr int R = K / 2;
+  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4;
+  const int grid = p.n * p.tiles_x * p.tiles_y;
+  k1_preprocess<K, HS><<<grid, K1_THREADS, smem, s>>>(p);
+  return cudaGetLastError();
+}
+
+template <int K, int HS>
+static cudaError_t config_k1() {
+  constexpr int R = K / 2;
+  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4;
+  return cudaFuncSetAttribute(k1_preprocess<K, HS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+
+#define NM03_K1_DISPATCH(FN, ...)                                                                   \
+  switch (median_window * 10 + sharpen_half) {                                                      \
+    case 31: return FN<3, 1>(__VA_ARGS__); case 32: return FN<3, 2>(__VA_ARGS__);                   \
+    case 33: return FN<3, 3>(__VA_ARGS__); case 34: return FN<3, 4>(__VA_ARGS__);                   \
+    case 51: return FN<5, 1>(__VA_ARGS__); case 52: return FN<5, 2>(__VA_ARGS__);                   \
+    case 53: return FN<5, 3>(__VA_ARGS__); case 54: return FN<5, 4>(__VA_ARGS__);                   \
+    case 71: return FN<7, 1>(__VA_ARGS__); case 72: return FN<7, 2>(__VA_ARGS__);                   \
+    case 73: return FN<7, 3>(__VA_ARGS__); case 74: return FN<7, 4>(__VA_ARGS__);                   \
+    default: return cudaErrorInvalidValue;                                                          \
+  }
+
+cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, cudaStream_t s) {
+  NM03_K1_DISPATCH(launch_k1, p, s)
+}
+
+// =================================================================================================
+// K23
+// =================================================================================================
+// Horizontal flood inside one 32-pixel word: spread the bits of c (c subset of p) along the runs of
+// ones of p, in both directions.  Adding c to p makes the carry ripple to the end of each run.
+__device__ __forceinline__ uint32_t hfill(uint32_t c, uint32_t p) {
+  const uint32_t up = ((p + c) ^ p) & p;
+  const uint32_t rp = __brev(p), rc = __brev(c);
+  const uint32_t dn = __brev(((rp + rc) ^ rp) & rp);
+  return up | dn | c;
+}
+
+__device__ __forceinline__ uint32_t spread4(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+// write 32 mask pixels (one word) as uint8 {0,1}
+__device__ __forceinline__ void store_word_u8(uint8_t* __restrict__ row, int x, int w, uint32_t bits, bool vec) {
+  if (vec && x + 32 <= w) {
+    uint4 a, b;
+    a.x = spread4(bits & 15u); a.y = spread4((bits >> 4) & 15u); a.z = spread4((bits >> 8) & 15u); a.w = spread4((bits >> 12) & 15u);
+    b.x = spread4((bits >> 16) & 15u); b.y = spread4((bits >> 20) & 15u); b.z = spread4((bits >> 24) & 15u); b.w = spread4(bits >> 28);
+    *reinterpret_cast<uint4*>(row + x) = a;
+    *reinterpret_cast<uint4*>(row + x + 16) = b;
+  } else {
+    for (int i = 0; i < 32 && x + i < w; ++i) row[x + i] = (bits >> i) & 1u;
+  }
+}
+
+// funnel: bits of the row shifted so that pixel x+s lands on x (s in -31..31), zeros from outside
+__device__ __forceinline__ uint32_t shifted(uint32_t l, uint32_t c, uint32_t r, int s) {
+  if (s == 0) return c;
+  if (s > 0) return (c >> s) | (r << (32 - s));   // pixel x+s -> x
+  return (c << (-s)) | (l >> (32 + s));           // pixel x-|s| -> x
+}
+
+__global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_constant__ SegParams p) {
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ __align__(16) uint32_t smem[];
+  const int wpr = p.wpr, rows = p.rows_per, C = p.cluster;
+  const int rank = C > 1 ? (int)cluster.block_rank() : 0;
+  const int slice = blockIdx.x / C;
+  const int tid = threadIdx.x;
+  // planes with SEG_HALO halo rows above and below: row index r (-HALO .. rows+HALO-1)
+  uint32_t* Pp = smem;                                   // [rows][wpr]
+  uint32_t* Mm = smem + (size_t)rows * wpr;              // [rows + 2*HALO][wpr]
+  __shared__ int s_flag[2];
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+  const int y_begin = rank * rows;                       // first image row owned
+  const int nrows = max(0, min(rows, p.h - y_begin));    // rows actually inside the image
+  const uint32_t* gp = p.pred + (size_t)slice * p.h * wpr;
+  const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
+
+  for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  for (int i = tid; i < rows * wpr; i += SEG_THREADS) {
+    const int r = i / wpr, k = i - r * wpr;
+    uint32_t v = r < nrows ? gp[(size_t)(y_begin + r) * wpr + k] : 0u;
+    if (k == wpr - 1) v &= lastmask;
+    Pp[i] = v;
+  }
+  __syncthreads();
+
+  int passes = 0;
+  if (p.do_fill) {
+    // ---- seeds ------------------------------------------------------------------------------
+    for (int i = tid; i < p.n_seeds; i += SEG_THREADS) {
+      const int sx = p.seeds[i].x, sy = p.seeds[i].y;
+      if (!p.host_mode) {
+        const int r = sy - y_begin;
+        if (r >= 0 && r < nrows) atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
+      } else {
+        // FAST executeOnHost: the seed's neighbours are tested, not the seed itself
+        const int ddx[8] = {0, 1, -1, 0, 1, -1, 1, -1}, ddy[8] = {1, 0, 0, -1, 1, 1, -1, -1};
+        for (int d = 0; d < (p.conn8 ? 8 : 4); ++d) {
+          const int nx = sx + ddx[d], ny = sy + ddy[d];
+          const int r = ny - y_begin;
+          if (nx < 0 || nx >= p.w || r < 0 || r >= nrows) continue;
+          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * wpr + (nx >> 5)]);
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- fill: sweep passes until nothing changes anywhere in the cluster --------------------
+    const bool masked = !p.border_expand && !p.host_mode;
+    const int nseg = (nrows + p.seg_rows - 1) / p.seg_rows;
+    for (;;) {
+      ++passes;
+      int changed = 0;
+      for (int it = tid; it < nseg * wpr; it += SEG_THREADS) {
+        const int sgi = it / wpr, k = it - sgi * wpr;
+        const int ra = sgi * p.seg_rows, rb = min(nrows, ra + p.seg_rows);
+        // interior-column mask of this word (pixels allowed to expand)
+        uint32_t colmask = 0xffffffffu;
+        if (masked) {
+          if (k == 0) colmask &= ~1u;
+          if (k == (p.w - 1) >> 5) colmask &= ~(1u << ((p.w - 1) & 31));
+        }
+#pragma unroll 1
+        for (int dir = 0; dir < 2; ++dir) {
+          int r = dir == 0 ? ra : rb - 1;
+          const int step = dir == 0 ? 1 : -1;
+          for (int cnt = ra; cnt < rb; ++cnt, r += step) {
+            const int y = y_begin + r;
+            const int rs = r - step;  // source row of this sweep direction
+            const int ro = r + step;  // the other vertical neighbour
+            auto src_row = [&](int rr, int kk) -> uint32_t {
+              if (kk < 0 || kk >= wpr) return 0u;
+              uint32_t v = MROW(rr)[kk];
+              if (masked) {
+                const int yy = y_begin + rr;
+                if (yy <= 0 || yy >= p.h - 1) return 0u;
+                if (kk == 0) v &= ~1u;
+                if (kk == (p.w - 1) >> 5) v &= ~(1u << ((p.w - 1) & 31));
+              }
+              return v;
+            };
+            const uint32_t pw = Pp[r * wpr + k];
+            const uint32_t m = MROW(r)[k];
+            uint32_t vs = src_row(rs, k) | src_row(ro, k);
+            if (p.conn8) {
+              const uint32_t a = src_row(rs, k), b = src_row(ro, k);
+              vs |= (a << 1) | (a >> 1) | (b << 1) | (b >> 1);
+              vs |= (src_row(rs, k - 1) >> 31) | (src_row(rs, k + 1) << 31);
+              vs |= (src_row(ro, k - 1) >> 31) | (src_row(ro, k + 1) << 31);
+            }
+            const uint32_t hz = (src_row(r, k - 1) >> 31) | (src_row(r, k + 1) << 31);
+            const uint32_t cand = m | ((vs | hz) & pw);
+            uint32_t rowmask = colmask;
+            if (masked && (y <= 0 || y >= p.h - 1)) rowmask = 0u;
+            const uint32_t f = hfill(cand & rowmask, pw & rowmask);
+            const uint32_t bnd = pw & ~rowmask & (cand | (f << 1) | (f >> 1));
+            const uint32_t nw = m | f | bnd;
+            if (nw != m) { MROW(r)[k] = nw; changed = 1; }
+          }
+        }
+      }
+      if (C == 1) {
+        if (!__syncthreads_or(changed)) break;
+      } else {
+        changed = __syncthreads_or(changed);
+        cluster.sync();  // every CTA finished its pass
+        // refresh the one halo row each side from the neighbouring CTAs; a change there is progress
+        int hchg = 0;
+        for (int k = tid; k < 2 * wpr; k += SEG_THREADS) {
+          const int side = k / wpr, kk = k - side * wpr;
+          const int nb = side == 0 ? rank - 1 : rank + 1;
+          if (nb < 0 || nb >= C) continue;
+          const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
+          const int rr = side == 0 ? rows - 1 : 0;          // neighbour's boundary row
+          const uint32_t v = remote[(size_t)(rr + SEG_HALO) * wpr + kk];
+          uint32_t* mine = MROW(side == 0 ? -1 : rows) + kk;
+          if (*mine != v) { *mine = v; hchg = 1; }
+        }
+        hchg = __syncthreads_or(hchg);
+        if (tid == 0) s_flag[0] = changed | hchg;
+        cluster.sync();  // flags written, halo reads done
+        int any = 0;
+        if (tid < C) any = *cluster.map_shared_rank(&s_flag[0], tid);
+        any = __syncthreads_or(any);
+        cluster.sync();  // everyone has read the flags before the next pass may rewrite them
+        if (!any) break;
+      }
+    }
+  } else {
+    for (int i = tid; i < rows * wpr; i += SEG_THREADS) MROW(0)[i] = Pp[i];
+    __syncthreads();
+  }
+  if (p.iterations && rank == 0 && tid == 0) p.iterations[slice] = passes;
+
+  // ---- halo rows of the final mask for the structuring element --------------------------------
+  const int nmax = max(p.dil_n, p.ero_n);
+  if (C > 1 && nmax > 0) {
+    cluster.sync();
+    for (int i = tid; i < 2 * nmax * wpr; i += SEG_THREADS) {
+      const int side = i / (nmax * wpr), j = i - side * nmax * wpr;
+      const int hr = j / wpr, kk = j - hr * wpr;
+      const int nb = side == 0 ? rank - 1 : rank + 1;
+      if (nb < 0 || nb >= C) continue;
+      const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
+      if (side == 0) MROW(-1 - hr)[kk] = remote[(size_t)(rows - 1 - hr + SEG_HALO) * wpr + kk];
+      else MROW(rows + hr)[kk] = remote[(size_t)(hr + SEG_HALO) * wpr + kk];
+    }
+    cluster.sync();  // nobody exits (or overwrites) while a neighbour still reads its rows
+  } else {
+    __syncthreads();
+  }
+
+  // ---- ImageCaster is the identity; dilation / erosion with the row-run form of the SE ---------
+  const bool vec = (p.w & 15) == 0;
+  for (int i = tid; i < nrows * wpr; i += SEG_THREADS) {
+    const int r = i / wpr, k = i - r * wpr;
+    const int y = y_begin + r;
+    const size_t rowoff = ((size_t)slice * p.h + y) * p.w;
+    const uint32_t m = MROW(r)[k];
+    if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
+    if (p.dilated) {
+      uint32_t acc = m;
+      if (p.dil_n > 0) {
+        acc = 0u;
+        for (int b = -p.dil_n; b <= p.dil_n; ++b) {
+          const int yy = y + b;
+          if (yy < 0 || yy >= p.h) continue;
+          const uint32_t* row = MROW(r + b);
+          const uint32_t c = row[k], l = k > 0 ? row[k - 1] : 0u, rr = k < wpr - 1 ? row[k + 1] : 0u;
+          const int hw = p.dil_hw[b + p.dil_n];
+          for (int s2 = -hw; s2 <= hw; ++s2) acc |= shifted(l, c, rr, s2);
+        }
+      }
+      store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+    }
+    if (p.eroded) {
+      uint32_t acc = m;
+      if (p.ero_n > 0) {
+        for (int b = -p.ero_n; b <= p.ero_n && acc; ++b) {
+          const int yy = y + b;
+          if (yy < 0 || yy >= p.h) { acc = 0u; break; }
+          const uint32_t* row = MROW(r + b);
+          const uint32_t c = row[k], l = k > 0 ? row[k - 1] : 0u, rr = k < wpr - 1 ? row[k + 1] : 0u;
+          const int hw = p.ero_hw[b + p.ero_n];
+          for (int s2 = -hw; s2 <= hw; ++s2) acc &= shifted(l, c, rr, s2);
+        }
+      }
+      store_word_u8(p.eroded + rowoff, k * 32, p.w, acc, vec);
+    }
+  }
+#undef MROW
+}
+
+size_t seg_smem_bytes(int rows_per, int wpr) {
+  return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * wpr * 4;
+}
+
+cudaError_t launch_segment(const SegParams& p, cudaStream_t s) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(p.n * p.cluster);
+  cfg.blockDim = dim3(SEG_THREADS);
+  cfg.dynamicSmemBytes = seg_smem_bytes(p.rows_per, p.wpr);
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = p.cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k23_segment, p);
+}
+
+// =================================================================================================
+// helpers for the per-operator entry points
+// =================================================================================================
+__global__ void k_threshold_pack(const float* __restrict__ img, int n, int w, int h, float lo, float hi,
+                                 uint32_t* __restrict__ bits) {
+  const int wpr = (w + 31) >> 5;
+  const long long total = (long long)n * h * wpr * 32;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long word = i >> 5;
+    const int x = (int)(word % wpr) * 32 + (int)(i & 31);
+    const long long row = word / wpr;
+    bool in = false;
+    if (x < w) { const float v = img[row * w + x]; in = v >= lo && v <= hi; }
+    const uint32_t b = __ballot_sync(0xffffffffu, in);
+    if ((i & 31) == 0) bits[word] = b;
+  }
+}
+
+__global__ void k_pack_u8(const uint8_t* __restrict__ mask, int n, int w, int h, uint32_t* __restrict__ bits) {
+  const int wpr = (w + 31) >> 5;
+  const long long total = (long long)n * h * wpr * 32;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long word = i >> 5;
+    const int x = (int)(word % wpr) * 32 + (int)(i & 31);
+    const long long row = word / wpr;
+    const bool in = x < w && mask[row * w + x] == 1;
+    const uint32_t b = __ballot_sync(0xffffffffu, in);
+    if ((i & 31) == 0) bits[word] = b;
+  }
+}
+
+static int grid_for(long long total) {
+  long long g = (total + 255) / 256;
+  return (int)(g < 1 ? 1 : (g > 148 * 16 ? 148 * 16 : g));
+}
+
+cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float lo, float hi, uint32_t* bits, cudaStream_t s) {
+  const long long total = (long long)n * h * ((w + 31) >> 5) * 32;
+  k_threshold_pack<<<grid_for(total), 256, 0, s>>>(img, n, w, h, lo, hi, bits);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* bits, cudaStream_t s) {
+  const long long total = (long long)n * h * ((w + 31) >> 5) * 32;
+  k_pack_u8<<<grid_for(total), 256, 0, s>>>(mask, n, w, h, bits);
+  return cudaGetLastError();
+}
+
+cudaError_t configure_kernels() {
+  cudaError_t e;
+  int median_window, sharpen_half;
+  for (median_window = 3; median_window <= 7; median_window += 2)
+    for (sharpen_half = 1; sharpen_half <= 4; ++sharpen_half) {
+      e = [&]() -> cudaError_t { NM03_K1_DISPATCH(config_k1) }();
+      if (e != cudaSuccess) return e;
+    }
+  e = cudaFuncSetAttribute(k23_segment, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 64);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(k23_segment, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
+}
+
+}  // namespace nm03

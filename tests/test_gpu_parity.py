@@ -1,0 +1,214 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.  Bit-exact for the median
+plane, the predicate, region-growing masks and morphology; the sharpen plane is compared both
+bit-exactly (the kernel mirrors the oracle's operation order) and against the stated tolerance
+(max abs error <= 1e-5 of the normalised range [0.5, 2.5], i.e. 2e-5)."""
+import numpy as np
+import pytest
+import scipy.ndimage as ndi
+
+import common as cm
+
+pytestmark = pytest.mark.gpu
+
+SHARPEN_TOL = 1e-5 * (2.5 - 0.5)
+
+
+@pytest.fixture(scope="module")
+def ctx(lib):
+    c = lib.Context([0])
+    yield c
+    c.close()
+
+
+def _cmp_pre(lib, ctx, raw, **kw):
+    h, w = raw.shape
+    got = ctx.preprocess(raw, lib.default_params(**kw))
+    rc, exp = cm.o_pipeline(raw, cm.oparams(**kw), want=("median", "sharpened"))
+    assert rc == 0
+    np.testing.assert_array_equal(got["median"], exp["median"])
+    assert np.max(np.abs(got["sharpened"] - exp["sharpened"])) <= SHARPEN_TOL
+    np.testing.assert_array_equal(got["sharpened"], exp["sharpened"])
+    p = cm.oparams(**kw)
+    pred = (exp["sharpened"] >= np.float32(p.rg_min)) & (exp["sharpened"] <= np.float32(p.rg_max))
+    np.testing.assert_array_equal(lib.unpack_predicate(got["predicate"], w), pred.astype(np.uint8))
+
+
+@pytest.mark.parametrize("w,h", [(256, 256), (128, 64), (130, 67), (100, 100), (517, 203), (512, 512)])
+def test_preprocess_shapes(lib, ctx, w, h):
+    _cmp_pre(lib, ctx, cm.phantom(w, h, 1, 3))
+
+
+@pytest.mark.parametrize("k", [3, 5, 7])
+@pytest.mark.parametrize("m", [3, 5, 7, 9])
+def test_preprocess_windows(lib, ctx, k, m):
+    _cmp_pre(lib, ctx, cm.phantom(160, 96, 2, k + m), median_window=k, sharpen_mask=m, sharpen_sigma=0.8)
+
+
+def test_preprocess_switches(lib, ctx):
+    raw = cm.phantom(200, 150, 4, 1)
+    _cmp_pre(lib, ctx, raw, sharpen_fma=1)
+    _cmp_pre(lib, ctx, raw, border_mode=1)
+    _cmp_pre(lib, ctx, raw, border_mode=1, sharpen_fma=1, median_window=5)
+
+
+def test_preprocess_full_int16_range_and_ties(lib, ctx):
+    rng = np.random.default_rng(0)
+    _cmp_pre(lib, ctx, rng.integers(-32768, 32768, (140, 133)).astype(np.int16))
+    _cmp_pre(lib, ctx, rng.integers(1195, 1206, (140, 133)).astype(np.int16))   # ties on the RG threshold
+    _cmp_pre(lib, ctx, np.full((120, 120), 1200, np.int16))                     # flat image exactly at rg_min
+    _cmp_pre(lib, ctx, np.full((120, 120), 2050, np.int16))
+
+
+def test_preprocess_uint16(lib, ctx):
+    rng = np.random.default_rng(1)
+    _cmp_pre(lib, ctx, rng.integers(0, 65536, (128, 160)).astype(np.uint16))
+    _cmp_pre(lib, ctx, cm.phantom(128, 160, 0, 0, dtype=np.uint16))
+
+
+# ---- region growing --------------------------------------------------------------------------
+def _rg_image(w, h, seed):
+    rng = np.random.default_rng(seed)
+    img = ndi.gaussian_filter(rng.uniform(0, 1, (h, w)), 3.0).astype(np.float32)
+    return ((img - img.min()) / (img.max() - img.min())).astype(np.float32)
+
+
+@pytest.mark.parametrize("w,h", [(256, 256), (130, 67), (512, 512), (1024, 1024), (33, 40), (700, 1300)])
+@pytest.mark.parametrize("conn", [4, 8])
+def test_region_grow_parity(lib, ctx, w, h, conn):
+    img = _rg_image(w, h, w + conn)
+    seeds = cm.o_make_seeds(w, h)
+    for mode in (0, 1):
+        for be in (1, 0):
+            kw = dict(rg_min=0.42, rg_max=0.58, rg_connectivity=conn, rg_mode=mode, rg_border_expand=be)
+            got, it = ctx.region_grow(img, seeds, lib.default_params(**kw))
+            rc, exp, _ = cm.o_region_grow(img, 0.42, 0.58, seeds, mode=mode, conn=conn, border_expand=be)
+            assert rc == 0 and it >= 1
+            np.testing.assert_array_equal(got, exp)
+
+
+def test_region_grow_serpentine_worst_case(lib, ctx):
+    """A one-pixel-wide spiral: geodesic distance ~ area/2, the hard case for convergence."""
+    h = w = 256
+    img = np.zeros((h, w), np.float32)
+    y0, y1, x0, x1 = 0, h - 1, 0, w - 1
+    while x0 < x1 and y0 < y1:
+        img[y0, x0:x1 + 1] = 0.8
+        img[y0:y1 + 1, x1] = 0.8
+        img[y1, x0 + 2:x1 + 1] = 0.8
+        img[y0 + 2:y1 + 1, x0 + 2] = 0.8
+        x0 += 4; y0 += 4; x1 -= 4; y1 -= 4  # noqa: E702
+    seeds = np.array([[0, 0]], np.int32)
+    got, it = ctx.region_grow(img, seeds, lib.default_params())
+    rc, exp, _ = cm.o_region_grow(img, 0.74, 0.91, seeds)
+    np.testing.assert_array_equal(got, exp)
+    assert exp.sum() > 5000
+
+
+def test_region_grow_errors(lib, ctx):
+    img = np.full((64, 64), 0.8, np.float32)
+    with pytest.raises(lib.Nm03Error) as e:
+        ctx.region_grow(img, np.array([[64, 1]], np.int32))
+    assert e.value.code == lib.ERR_SEED_OOB
+    with pytest.raises(lib.Nm03Error) as e:
+        ctx.region_grow(img, np.zeros((0, 2), np.int32))
+    assert e.value.code == lib.ERR_NO_SEEDS
+
+
+# ---- morphology ------------------------------------------------------------------------------
+@pytest.mark.parametrize("w,h", [(256, 256), (130, 67), (512, 512), (1024, 1024), (31, 9)])
+@pytest.mark.parametrize("size", [3, 5, 7, 15])
+def test_morphology_parity(lib, ctx, w, h, size):
+    rng = np.random.default_rng(size)
+    m = (ndi.gaussian_filter(rng.uniform(0, 1, (h, w)), 2.0) > 0.5).astype(np.uint8)
+    m[: h // 8, : w // 8] = 1
+    m[-1, :] = 1
+    for se in (0, 1):
+        np.testing.assert_array_equal(ctx.morphology(m, size, se, 0), cm.o_dilate(m, size, se)[1])
+        np.testing.assert_array_equal(ctx.morphology(m, size, se, 1), cm.o_erode(m, size, se)[1])
+
+
+def test_morphology_treats_only_one_as_foreground(lib, ctx):
+    m = np.zeros((40, 40), np.uint8)
+    m[10, 10] = 1
+    m[30, 30] = 2   # FAST tests == 1
+    np.testing.assert_array_equal(ctx.morphology(m, 3, 0, 0), cm.o_dilate(m, 3)[1])
+
+
+def test_morphology_errors(lib, ctx):
+    m = np.zeros((40, 40), np.uint8)
+    for size in (2, 1, 4):
+        with pytest.raises(lib.Nm03Error) as e:
+            ctx.morphology(m, size)
+        assert e.value.code == lib.ERR_PARAM
+
+
+# ---- whole pipeline --------------------------------------------------------------------------
+WANT = ("dilated", "eroded", "rg_mask", "sharpened", "median", "rg_iterations")
+
+
+def _cmp_pipeline(lib, ctx, raws, **kw):
+    res = ctx.process_batch(raws, lib.default_params(**kw), want=WANT)
+    for i in range(len(raws)):
+        rc, exp = cm.o_pipeline(raws[i], cm.oparams(**kw))
+        assert rc == 0
+        for name in ("median", "sharpened", "rg_mask", "dilated") + (("eroded",) if kw.get("erode_size", 0) else ()):
+            np.testing.assert_array_equal(res[name][i], exp[name], err_msg=f"slice {i} {name}")
+        assert res["rg_iterations"][i] >= 1
+    return res
+
+
+def test_pipeline_c1_test_path_256(lib, ctx):
+    """BASELINE config 1: one 256x256 slice through all stages incl. the erosion branch."""
+    res = _cmp_pipeline(lib, ctx, np.stack([cm.phantom(256, 256, 17, 14)]), erode_size=3)
+    assert 0 < res["dilated"].sum() < res["dilated"].size
+
+
+def test_pipeline_c2_series_512(lib, ctx):
+    """BASELINE config 2 (reduced to 6 slices for the oracle's runtime): 512x512 default params."""
+    raws = np.stack([cm.phantom(512, 512, 0, i) for i in range(6)])
+    res = _cmp_pipeline(lib, ctx, raws)
+    assert all(res["dilated"][i].sum() > 0 for i in range(6))
+
+
+def test_pipeline_c4_large_matrix(lib, ctx):
+    """BASELINE config 4 shape: 1024x1024, median window 5, dilation size 7 (radius 3)."""
+    _cmp_pipeline(lib, ctx, np.stack([cm.phantom(1024, 1024, 3, i) for i in range(2)]), median_window=5, dilate_size=7)
+
+
+def test_pipeline_c5_lowcontrast(lib, ctx):
+    """BASELINE config 5: grown region covers >50% of each slice."""
+    raws = np.stack([cm.phantom(512, 512, 5, i, kind="lowcontrast") for i in range(2)])
+    res = _cmp_pipeline(lib, ctx, raws)
+    assert res["rg_mask"].mean() > 0.5
+
+
+def test_pipeline_ragged_and_switches(lib, ctx):
+    raws = np.stack([cm.phantom(333, 205, 6, i) for i in range(3)])
+    _cmp_pipeline(lib, ctx, raws, erode_size=5, rg_connectivity=8, se_shape=1, sharpen_fma=1)
+    _cmp_pipeline(lib, ctx, raws, rg_mode=1, border_mode=1, rg_border_expand=0)
+
+
+def test_pipeline_dimension_guard(lib, ctx):
+    with pytest.raises(lib.Nm03Error) as e:
+        ctx.process_batch(np.zeros((2, 99, 300), np.int16))
+    assert e.value.code == lib.ERR_TOO_SMALL
+    assert "Image dimensions too small: 300x99" in str(e.value)
+
+
+def test_pipeline_size_independent_properties_full_c2(lib, ctx):
+    """Full 24-slice series: idempotence of the fill, dilate ⊇ mask ⊇ erode, determinism."""
+    raws = np.stack([cm.phantom(512, 512, 1, i) for i in range(24)])
+    a = ctx.process_batch(raws, lib.default_params(erode_size=3), want=WANT)
+    b = ctx.process_batch(raws, lib.default_params(erode_size=3), want=WANT)
+    for k in ("dilated", "eroded", "rg_mask"):
+        np.testing.assert_array_equal(a[k], b[k])
+    assert np.all(a["dilated"] >= a["rg_mask"]) and np.all(a["rg_mask"] >= a["eroded"])
+    seeds = lib.make_seeds(512, 512)
+    for i in (0, 11, 23):
+        pred = ((a["sharpened"][i] >= np.float32(0.74)) & (a["sharpened"][i] <= np.float32(0.91)))
+        assert np.all(pred[a["rg_mask"][i] == 1])                       # mask inside the predicate
+        again, _ = ctx.region_grow(a["sharpened"][i], seeds)              # fill is idempotent
+        np.testing.assert_array_equal(again, a["rg_mask"][i])
+        lab, _ = ndi.label(pred)
+        ids = {lab[y, x] for x, y in seeds if lab[y, x]}
+        np.testing.assert_array_equal(a["rg_mask"][i], np.isin(lab, list(ids)).astype(np.uint8))
