@@ -134,6 +134,13 @@ int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, i
 /* ---- introspection for benchmarks ------------------------------------------------------------- */
 /* Number of kernel launches this library has issued on `gpu` since nm03_init. */
 long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu);
+/* Per-kernel device timing of the whole-pipeline entry points (CUDA events on the launching stream,
+ * recorded around each kernel).  No counterpart in the reference, which ships no profiling hooks
+ * (README.md:92-96 names external tools only).  nm03_profile_read waits for the recorded work,
+ * returns the summed milliseconds of the preprocess and segment kernels and the number of
+ * pipeline calls since the last read, and resets the sums. */
+int nm03_profile_enable(nm03_ctx* ctx, int gpu, int on);
+int nm03_profile_read(nm03_ctx* ctx, int gpu, double* preprocess_ms, double* segment_ms, long long* calls);
 
 #ifdef __cplusplus
 }

@@ -19,6 +19,7 @@ EXPORTS = [
     "nm03_init", "nm03_shutdown", "nm03_last_error", "nm03_version", "nm03_gpu_count", "nm03_default_params",
     "nm03_make_seeds", "nm03_process_batch", "nm03_process_batch_device", "nm03_host_alloc", "nm03_host_free",
     "nm03_preprocess", "nm03_region_grow", "nm03_morphology", "nm03_kernel_launches",
+    "nm03_profile_enable", "nm03_profile_read",
 ]
 
 OK = 0
@@ -69,6 +70,8 @@ def lib():
         _lib.nm03_last_error.restype = C.c_char_p
         _lib.nm03_kernel_launches.restype = C.c_longlong
         _lib.nm03_kernel_launches.argtypes = [C.c_void_p, C.c_int]
+        _lib.nm03_profile_enable.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        _lib.nm03_profile_read.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.nm03_shutdown.argtypes = [C.c_void_p]
         _lib.nm03_shutdown.restype = None
         _lib.nm03_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
@@ -137,6 +140,26 @@ class Context:
 
     def kernel_launches(self, gpu=0):
         return lib().nm03_kernel_launches(self._h, gpu)
+
+    def profile_enable(self, on=True, gpu=0):
+        _check(lib().nm03_profile_enable(self._h, gpu, int(on)))
+
+    def profile_read(self, gpu=0):
+        """(preprocess_ms, segment_ms, calls) summed since the last read."""
+        a, b, n = C.c_double(0), C.c_double(0), C.c_longlong(0)
+        _check(lib().nm03_profile_read(self._h, gpu, C.byref(a), C.byref(b), C.byref(n)))
+        return a.value, b.value, n.value
+
+    def host_alloc(self, shape, dtype):
+        """numpy array backed by pinned host memory (nm03_host_alloc)."""
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        _check(lib().nm03_host_alloc(C.byref(p), nbytes))
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        self._pinned = getattr(self, "_pinned", [])
+        self._pinned.append(p)
+        return arr
 
     # ---- whole pipeline, host buffers -------------------------------------------------------
     def process_batch(self, slices, params=None, seeds=None, want=("dilated",), gpu=0, out=None):

@@ -49,12 +49,19 @@ struct Slot {
   bool busy = false;
 };
 
+struct ProfRec {
+  cudaEvent_t e[3] = {nullptr, nullptr, nullptr};  // before K1, between, after K23
+};
+
 struct Worker {
   int device = 0;
   Slot slots[kSlots];
   std::mutex mu;
   std::condition_variable cv;
   std::atomic<long long> launches{0};
+  std::atomic<int> profiling{0};
+  std::mutex prof_mu;
+  std::vector<ProfRec> prof_pending, prof_free;
 };
 
 }  // namespace
@@ -281,13 +288,27 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
   pre.predicate = s->pred;
+  ProfRec rec;
+  const bool prof = wk->profiling.load() != 0;
+  if (prof) {
+    std::lock_guard<std::mutex> lk(wk->prof_mu);
+    if (!wk->prof_free.empty()) { rec = wk->prof_free.back(); wk->prof_free.pop_back(); }
+    else for (auto& e : rec.e) CK(cudaEventCreate(&e));
+  }
+  if (prof) CK(cudaEventRecord(rec.e[0], st));
   CK(nm03::launch_preprocess(pre, p->median_window, hs, st));
+  if (prof) CK(cudaEventRecord(rec.e[1], st));
   seg.pred = s->pred;
   seg.dilated = d_out->dilated;
   seg.eroded = (p->erode_size > 0) ? d_out->eroded : nullptr;
   seg.rg_mask = d_out->rg_mask;
   seg.iterations = d_out->rg_iterations;
   CK(nm03::launch_segment(seg, st));
+  if (prof) {
+    CK(cudaEventRecord(rec.e[2], st));
+    std::lock_guard<std::mutex> lk(wk->prof_mu);
+    wk->prof_pending.push_back(rec);
+  }
   wk->launches += 2;
   CK(cudaEventRecord(s->done, st));
   s->used = true;
@@ -382,6 +403,9 @@ void nm03_shutdown(nm03_ctx* ctx) {
   if (!ctx) return;
   for (Worker* wk : ctx->workers) {
     DeviceGuard g(wk->device);
+    for (auto* v : {&wk->prof_pending, &wk->prof_free})
+      for (auto& rec : *v)
+        for (auto& e : rec.e) if (e) cudaEventDestroy(e);
     for (auto& s : wk->slots) {
       if (s.stream) cudaStreamSynchronize(s.stream);
       if (s.pred) cudaFree(s.pred);
@@ -400,6 +424,37 @@ int nm03_gpu_count(const nm03_ctx* ctx) { return ctx ? (int)ctx->workers.size() 
 long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu) {
   if (!ctx || gpu < 0 || gpu >= (int)ctx->workers.size()) return -1;
   return ctx->workers[gpu]->launches.load();
+}
+
+int nm03_profile_enable(nm03_ctx* ctx, int gpu, int on) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  wk->profiling.store(on ? 1 : 0);
+  return NM03_OK;
+}
+
+int nm03_profile_read(nm03_ctx* ctx, int gpu, double* preprocess_ms, double* segment_ms, long long* calls) {
+  Worker* wk;
+  int rc;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  DeviceGuard g(wk->device);
+  std::lock_guard<std::mutex> lk(wk->prof_mu);
+  double a = 0.0, b = 0.0;
+  long long n = 0;
+  for (auto& rec : wk->prof_pending) {
+    CK(cudaEventSynchronize(rec.e[2]));
+    float t1 = 0.f, t2 = 0.f;
+    CK(cudaEventElapsedTime(&t1, rec.e[0], rec.e[1]));
+    CK(cudaEventElapsedTime(&t2, rec.e[1], rec.e[2]));
+    a += t1; b += t2; ++n;
+    wk->prof_free.push_back(rec);
+  }
+  wk->prof_pending.clear();
+  if (preprocess_ms) *preprocess_ms = a;
+  if (segment_ms) *segment_ms = b;
+  if (calls) *calls = n;
+  return NM03_OK;
 }
 
 int nm03_host_alloc(void** p, size_t bytes) {
