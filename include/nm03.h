@@ -112,6 +112,42 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
                               const nm03_params* params, const int* seeds_xy, int n_seeds,
                               const nm03_outputs* d_out, void* stream);
 
+/* Whole pipeline on device buffers for callers that must not allocate.  This entry point has no
+ * counterpart in the reference (FAST allocates freely inside every update()).
+ *
+ * Who needs it: a host thread that feeds one GPU stream while other streams of the same process are
+ * busy.  cudaMalloc and cudaFree are not ordinary calls there: they take the driver's allocator lock
+ * and wait for the whole device, so one allocation in a feeder thread stalls every other feeder's
+ * copies and kernels.  The same holds for a process whose device memory has been handed out in full
+ * to a pool owned by another component (an inference server, a framework's caching allocator): a
+ * late cudaMalloc there simply fails.  Such callers cannot use nm03_process_batch_device, whose
+ * predicate bit-plane (the scratch that carries the range test from the preprocess kernel to the
+ * region-growing kernel) is grown with cudaMalloc on demand.
+ *
+ * Here that scratch is a fixed array inside the library image: NM03_NOALLOC_MAX_PRED_WORDS 32-bit words
+ * (1 MiB) of device memory on every GPU that loads libnm03.so, held until the process exits.  The
+ * call itself performs no cudaMalloc, cudaFree, stream/event creation or any other allocating
+ * routine; inputs and outputs are the caller's device buffers, exactly as for
+ * nm03_process_batch_device, and the work is queued on `stream` (NULL = the default stream) without
+ * waiting for it.
+ *
+ * Limit: n * h * ceil(w/32) must not exceed NM03_NOALLOC_MAX_PRED_WORDS (32 slices of 512x512, 8 of
+ * 1024x1024); larger batches are refused with NM03_ERR_TOO_LARGE and must be split by the caller.
+ *
+ * First call: the first call on each GPU looks up the device address of the array (with that GPU
+ * current) and caches it.  Make that first call during start-up, before any stream capture begins.
+ *
+ * Sharing: every call on a GPU uses the same array, and it keeps whatever the previous call left.
+ * Nothing in it has to start at zero — the preprocess kernel overwrites every word the
+ * region-growing kernel will read — so no clearing pass is issued.  Two calls whose kernels can
+ * overlap on the GPU (different streams without an ordering between them, or different host
+ * threads) race on the array and produce wrong masks; order such calls on one stream or with
+ * events. */
+#define NM03_NOALLOC_MAX_PRED_WORDS (256 * 1024)
+int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,
+                                      const nm03_params* params, const int* seeds_xy, int n_seeds,
+                                      const nm03_outputs* d_out, void* stream);
+
 /* Pinned host memory for zero-copy staging of nm03_process_batch inputs/outputs. */
 int nm03_host_alloc(void** p, size_t bytes);
 int nm03_host_free(void* p);

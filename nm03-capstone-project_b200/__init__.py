@@ -19,8 +19,10 @@ EXPORTS = [
     "nm03_init", "nm03_shutdown", "nm03_last_error", "nm03_version", "nm03_gpu_count", "nm03_default_params",
     "nm03_make_seeds", "nm03_process_batch", "nm03_process_batch_device", "nm03_host_alloc", "nm03_host_free",
     "nm03_preprocess", "nm03_region_grow", "nm03_morphology", "nm03_kernel_launches",
-    "nm03_profile_enable", "nm03_profile_read",
+    "nm03_profile_enable", "nm03_profile_read", "nm03_process_batch_device_noalloc",
 ]
+
+NOALLOC_MAX_PRED_WORDS = 256 * 1024  # NM03_NOALLOC_MAX_PRED_WORDS
 
 OK = 0
 ERR_INVALID, ERR_TOO_SMALL, ERR_PARAM, ERR_NO_SEEDS, ERR_SEED_OOB = -1, -2, -3, -4, -5
@@ -80,6 +82,7 @@ def lib():
                                             C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         _lib.nm03_process_batch_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                    C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        _lib.nm03_process_batch_device_noalloc.argtypes = _lib.nm03_process_batch_device.argtypes
         _lib.nm03_preprocess.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p]
         _lib.nm03_region_grow.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
@@ -194,6 +197,14 @@ class Context:
         _check(lib().nm03_process_batch_device(self._h, gpu, C.c_void_p(d_slices_ptr), n, w, h, C.byref(params),
                                                _p(sp), 0 if sp is None else len(sp), C.byref(d_out),
                                                C.c_void_p(stream)))
+
+    def process_batch_device_noalloc(self, d_slices_ptr, n, w, h, params, d_out: Outputs, stream=0, seeds=None, gpu=0):
+        """nm03_process_batch_device_noalloc: same as process_batch_device, but the scratch bit-plane is
+        the library's built-in 1 MiB array, so the call allocates nothing (see include/nm03.h)."""
+        sp = None if seeds is None else np.ascontiguousarray(seeds, np.int32)
+        _check(lib().nm03_process_batch_device_noalloc(self._h, gpu, C.c_void_p(d_slices_ptr), n, w, h,
+                                                       C.byref(params), _p(sp), 0 if sp is None else len(sp),
+                                                       C.byref(d_out), C.c_void_p(stream)))
 
     # ---- per-operator entry points ----------------------------------------------------------
     def preprocess(self, raw, params=None, want=("median", "sharpened", "predicate"), gpu=0):

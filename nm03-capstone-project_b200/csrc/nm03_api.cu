@@ -317,7 +317,89 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
 
 }  // namespace
 
+// ---- scratch of the no-allocation entry point ------------------------------------------------
+// The predicate bit-plane of nm03_process_batch_device_noalloc lives in the library image instead of
+// in cudaMalloc'ed memory.  In host code `g_noalloc_pred` is only a handle for the symbol, not a
+// device address: the address is asked for once per device, with that device current, and cached.
+static __device__ __align__(256) uint32_t g_noalloc_pred[NM03_NOALLOC_MAX_PRED_WORDS];
+
+namespace {
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_addr[kNoallocMaxDevices] = {};  // device address per CUDA ordinal, null = not looked up yet
+
+// caller has made `device` current
+int noalloc_scratch(int device, uint32_t** out) {
+  if (device < 0 || device >= kNoallocMaxDevices)
+    return fail(NM03_ERR_UNSUPPORTED, "device ordinal %d is beyond the %d the no-allocation path tracks", device,
+                kNoallocMaxDevices);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_addr[device]) {
+    uint32_t* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_pred);
+    if (e != cudaSuccess || !ptr)
+      return fail(NM03_ERR_CUDA, "cudaGetSymbolAddress(built-in scratch) failed on device %d: %s", device,
+                  cudaGetErrorString(e));
+    g_noalloc_addr[device] = ptr;
+  }
+  *out = g_noalloc_addr[device];
+  return NM03_OK;
+}
+
+}  // namespace
+
 extern "C" {
+
+// See include/nm03.h for the contract.  No cudaMalloc/cudaFree, no stream or event creation, no slot
+// lease (the slots' scratch is what this variant avoids); the only state touched is the cached symbol
+// address and the launch counter.
+int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,
+                                      const nm03_params* params, const int* seeds_xy, int n_seeds,
+                                      const nm03_outputs* d_out, void* stream) {
+  Worker* wk;
+  int rc, hs = 0;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!d_slices || !d_out || n < 0) return fail(NM03_ERR_INVALID, "null buffer or negative count");
+  if (n == 0) return NM03_OK;
+  if ((rc = check_params(params, w, h, true))) return rc;
+  if ((rc = check_preprocess(params, &hs))) return rc;
+  const long long wpr = (w + 31) / 32;
+  const long long words = (long long)n * h * wpr;
+  if (words > (long long)NM03_NOALLOC_MAX_PRED_WORDS) {
+    const long long per_slice = (long long)h * wpr;
+    return fail(NM03_ERR_TOO_LARGE,
+                "batch of %d slices %dx%d needs %lld words of predicate scratch but the built-in array holds %d; "
+                "pass at most %lld slices of this size per call",
+                n, w, h, words, (int)NM03_NOALLOC_MAX_PRED_WORDS,
+                per_slice > 0 ? (long long)NM03_NOALLOC_MAX_PRED_WORDS / per_slice : 0LL);
+  }
+  nm03::PreParams pre;
+  if ((rc = fill_pre(pre, params, n, w, h, hs))) return rc;
+  nm03::SegParams seg;
+  if ((rc = fill_seg(seg, params, n, w, h, seeds_xy, n_seeds, true))) return rc;
+  if ((rc = se_halfwidths(params->dilate_size, params->se_shape, &seg.dil_n, seg.dil_hw))) return rc;
+  if (params->erode_size > 0 && d_out->eroded) {
+    if ((rc = se_halfwidths(params->erode_size, params->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
+  }
+  DeviceGuard g(wk->device);
+  uint32_t* scratch = nullptr;
+  if ((rc = noalloc_scratch(wk->device, &scratch))) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  pre.in = d_slices;
+  pre.median = d_out->median;
+  pre.sharpened = d_out->sharpened;
+  pre.predicate = scratch;
+  CK(nm03::launch_preprocess(pre, params->median_window, hs, st));
+  seg.pred = scratch;
+  seg.dilated = d_out->dilated;
+  seg.eroded = (params->erode_size > 0) ? d_out->eroded : nullptr;
+  seg.rg_mask = d_out->rg_mask;
+  seg.iterations = d_out->rg_iterations;
+  CK(nm03::launch_segment(seg, st));
+  wk->launches += 2;
+  return NM03_OK;
+}
 
 const char* nm03_last_error(void) { return g_err; }
 int nm03_version(void) { return 100; }
