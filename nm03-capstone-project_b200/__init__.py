@@ -239,6 +239,14 @@ class Context:
         return out
 
 
+def shard_range(n_items, world, rank):
+    """Contiguous patient-range sharding: GPU g of G gets items [floor(g*P/G), floor((g+1)*P/G)).
+    The reference's analogue is the sorted patient list walked by one process (main_parallel.cpp:248,373)."""
+    if world <= 0 or not 0 <= rank < world:
+        raise ValueError("bad world/rank")
+    return (rank * n_items) // world, ((rank + 1) * n_items) // world
+
+
 def unpack_predicate(pred, w):
     """bit-plane (h, ceil(w/32)) uint32 -> (h, w) uint8."""
     bits = np.unpackbits(pred.view(np.uint8).reshape(pred.shape[0], -1), axis=1, bitorder="little")
