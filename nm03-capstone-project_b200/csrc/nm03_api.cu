@@ -12,6 +12,7 @@
 #include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -35,6 +36,10 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 constexpr int kSlots = 4;
+
+// NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
+// predicate is needed (A/B measurements; results are identical by construction)
+const bool g_force_exact = [] { const char* e = getenv("NM03_FORCE_EXACT_SHARPEN"); return e && e[0] == '1'; }();
 
 struct Slot {
   cudaStream_t stream = nullptr;
@@ -187,7 +192,69 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
     }
   for (int i = 0; i < m * m; ++i) k.mask[i] /= sum;
   for (int i = m * m; i < 81; ++i) k.mask[i] = 0.0f;
+  for (int i = 0; i < 9; ++i) k.gx[i] = 0.0f;
+  k.ea = k.eb = k.ec = 0.0f;
   return NM03_OK;
+}
+
+// Fast predicate mode of K1 (used when the sharpened plane itself is not requested).
+//
+// The kernel evaluates blur_a = sum_y gx[y] * (sum_x gx[x] * v) over |x|,|y| <= he with FMAs, and
+// sharpened_a = v + gain*(v - blur_a).  The oracle's value uses the full m x m mask accumulated tap by
+// tap.  With u = 2^-24, gamma_n = n*u/(1-n*u), w = the fp32 mask, S_in = sum_inside w|v|,
+//   |blur_a - blur_exact| <= [gamma_{m*m} + gamma_{2(2he+1)}(1+rho) + rho] * S_in
+//                            + [(1+gamma_{m*m}) * D_out + D_abs] * Vmax
+// where rho bounds |gx[x]gx[y] - w|/w over the significant inside taps, D_abs collects the others,
+// D_out is the mask mass outside the (2he+1)^2 window and Vmax bounds |f|.  If f >= 0 everywhere then
+// S_in <= blur_a * (1 + 2 rho + 4 gamma), otherwise S_in <= Vmax.  The three rounded operations after
+// the blur add u*(6|gain|(|v|+|blur|) + 2|v|).  Everything is evaluated in double and inflated by 5 %.
+// A pixel whose fast value is farther than eps = ea*|blur_a| + eb*|v| + ec from both thresholds has
+// the same predicate bit as the oracle; the others are recomputed exactly in the kernel.
+// Returns the chosen K1 mode.
+int fill_fast(nm03::PreParams& k, const nm03_params* p, int sharpen_half) {
+  const int hs = sharpen_half, m = 2 * hs + 1;
+  // separable factors in fp32
+  float g[9], gs = 0.0f;
+  for (int x = -hs; x <= hs; ++x) { g[x + hs] = expf(-(float)(x * x) / (2.0f * p->sharpen_sigma * p->sharpen_sigma)); gs += g[x + hs]; }
+  for (int x = -hs; x <= hs; ++x) k.gx[x + nm03::K1_HS_MAX] = g[x + hs] / gs;
+  const double lo = f_host(p->input_unsigned ? 0.0f : -32768.0f, p), hi = f_host(p->input_unsigned ? 65535.0f : 32767.0f, p);
+  const double vmax = std::fmax(std::fabs(lo), std::fabs(hi));
+  const bool nonneg = lo >= 0.0 && hi >= 0.0;
+  const double u = 1.0 / 16777216.0;
+  auto gamma = [&](double n) { return n * u / (1.0 - n * u); };
+  const double gain = std::fabs((double)p->sharpen_gain);
+  int best_mode = nm03::K1_FAST_FULL;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const int he = (attempt == 0 && hs > 2) ? 2 : hs;
+    if (attempt == 1 && hs <= 2 && best_mode == nm03::K1_FAST_FULL && k.ea != 0.0f) break;
+    double rho = 0.0, d_abs = 0.0, d_out = 0.0;
+    for (int x = -hs; x <= hs; ++x)
+      for (int y = -hs; y <= hs; ++y) {
+        const double wxy = k.mask[x + hs + (y + hs) * m];
+        if (std::abs(x) <= he && std::abs(y) <= he) {
+          const double sep = (double)k.gx[x + nm03::K1_HS_MAX] * (double)k.gx[y + nm03::K1_HS_MAX];
+          if (wxy >= 1e-12) rho = std::fmax(rho, std::fabs(sep - wxy) / wxy);
+          else d_abs += std::fabs(sep - wxy);
+        } else {
+          d_out += wxy;
+        }
+      }
+    const double gM = gamma(m * m), g2 = gamma(2.0 * (2 * he + 1));
+    double c1 = gM + g2 * (1.0 + rho) + rho;
+    const double c2 = ((1.0 + gM) * d_out + d_abs) * vmax * 1.05;
+    double ea, ec = gain * c2;
+    if (nonneg) { c1 *= (1.0 + 2.0 * rho + 4.0 * g2) * 1.05; ea = gain * c1 + 6.3 * u * gain; }
+    else { ec += gain * c1 * vmax * 1.05; ea = 6.3 * u * gain; }
+    const double eb = u * (6.3 * gain + 2.1);
+    // the truncated window is only worth it when it does not widen the band noticeably
+    if (attempt == 0 && hs > 2 && ec > 4e-6) continue;
+    k.ea = (float)(ea * 1.02) + 1e-12f;
+    k.eb = (float)(eb * 1.02) + 1e-12f;
+    k.ec = (float)(ec * 1.02) + 1e-12f;
+    best_mode = (he < hs) ? nm03::K1_FAST_HE2 : nm03::K1_FAST_FULL;
+    break;
+  }
+  return best_mode;
 }
 
 int se_halfwidths(int size, int se_shape, int* n_out, int8_t* hw) {
@@ -288,6 +355,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
   pre.predicate = s->pred;
+  const int k1_mode = (d_out->sharpened || g_force_exact) ? nm03::K1_EXACT : fill_fast(pre, p, hs);
   ProfRec rec;
   const bool prof = wk->profiling.load() != 0;
   if (prof) {
@@ -296,7 +364,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
     else for (auto& e : rec.e) CK(cudaEventCreate(&e));
   }
   if (prof) CK(cudaEventRecord(rec.e[0], st));
-  CK(nm03::launch_preprocess(pre, p->median_window, hs, st));
+  CK(nm03::launch_preprocess(pre, p->median_window, hs, k1_mode, st));
   if (prof) CK(cudaEventRecord(rec.e[1], st));
   seg.pred = s->pred;
   seg.dilated = d_out->dilated;
@@ -390,7 +458,8 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
   pre.predicate = scratch;
-  CK(nm03::launch_preprocess(pre, params->median_window, hs, st));
+  const int k1_mode = (d_out->sharpened || g_force_exact) ? nm03::K1_EXACT : fill_fast(pre, params, hs);
+  CK(nm03::launch_preprocess(pre, params->median_window, hs, k1_mode, st));
   seg.pred = scratch;
   seg.dilated = d_out->dilated;
   seg.eroded = (params->erode_size > 0) ? d_out->eroded : nullptr;
@@ -675,7 +744,8 @@ int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, con
   pre.median = median ? (float*)so : nullptr;
   pre.sharpened = sharpened ? (float*)(so + npx * 4) : nullptr;
   pre.predicate = predicate ? (uint32_t*)(so + npx * 8) : nullptr;
-  CK(nm03::launch_preprocess(pre, params->median_window, hs, s->stream));
+  const int k1_mode = (sharpened || g_force_exact) ? nm03::K1_EXACT : fill_fast(pre, params, hs);
+  CK(nm03::launch_preprocess(pre, params->median_window, hs, k1_mode, s->stream));
   wk->launches += 1;
   if (median) CK(cudaMemcpyAsync(median, pre.median, npx * 4, cudaMemcpyDeviceToHost, s->stream));
   if (sharpened) CK(cudaMemcpyAsync(sharpened, pre.sharpened, npx * 4, cudaMemcpyDeviceToHost, s->stream));

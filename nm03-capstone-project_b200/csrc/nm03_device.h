@@ -30,7 +30,14 @@ struct PreParams {
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
   float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
+  // fast predicate path (no sharpened plane requested): separable blur with taps gx[-he..he] and a
+  // proven bound eps = ea*|blur| + eb*|v| + ec on |sharpened_fast - sharpened_exact|; pixels closer
+  // than eps to a threshold are recomputed in the oracle's exact order.
+  float gx[9];
+  float ea, eb, ec;
 };
+
+enum { K1_EXACT = 0, K1_FAST_FULL = 1, K1_FAST_HE2 = 2 };  // sharpen evaluation mode
 
 // ---- K2+K3: flood fill + morphology on bit-packed planes, one thread-block cluster per slice ----
 constexpr int SEG_THREADS = 256;
@@ -59,7 +66,7 @@ struct SegParams {
 size_t seg_smem_bytes(int rows_per, int wpr);
 
 // launchers (return cudaError_t of the launch)
-cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, cudaStream_t s);
+cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, int mode, cudaStream_t s);
 cudaError_t launch_segment(const SegParams& p, cudaStream_t s);
 cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float lo, float hi, uint32_t* bits,
                                   cudaStream_t s);

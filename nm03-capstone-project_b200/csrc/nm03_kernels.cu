@@ -106,7 +106,25 @@ __device__ __forceinline__ void blur4(const float* __restrict__ Mrow0, int mws, 
   }
 }
 
-template <int K, int HS>
+// Exact blur of ONE pixel in the oracle's order (slow path of the fast mode; rare).
+template <int HS>
+__device__ __noinline__ float blur1_exact(const float* __restrict__ Mc, const PreParams& p) {
+  constexpr int m = 2 * HS + 1;
+  float acc = 0.0f;
+#pragma unroll 1
+  for (int xi = 0; xi < m; ++xi) {
+#pragma unroll
+    for (int yi = 0; yi < m; ++yi) {
+      const float v = Mc[(yi - HS) * K1_MW + (xi - HS)];
+      const float wgt = p.mask[xi + yi * m];
+      if (p.use_fma) acc = __fmaf_rn(wgt, v, acc);
+      else acc = __fadd_rn(acc, __fmul_rn(wgt, v));
+    }
+  }
+  return acc;
+}
+
+template <int K, int HS, int MODE>
 __global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_constant__ PreParams p) {
   constexpr int R = K / 2;
   constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
@@ -192,8 +210,10 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_cons
     __syncthreads();
   }
 
-  // ---- phase C: unsharp mask, range predicate, stores (one warp = one 128-pixel output row) ----
+  // ---- phase C: unsharp mask, range predicate, stores ------------------------------------------
   const int lane = tid & 31;
+  if (MODE == K1_EXACT) {
+  // every pixel in the oracle's exact operation order (one warp = one 128-pixel output row)
   for (int it = tid; it < K1_TH * (K1_TW / 4); it += K1_THREADS) {
     const int oyl = it / (K1_TW / 4), xq = it - oyl * (K1_TW / 4);
     const int oy = y0 + oyl, ox = x0 + 4 * xq;
@@ -235,22 +255,94 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_cons
       if (wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = word;
     }
   }
+  } else {
+    // Fast predicate: separable (2*HE+1)-tap blur shared down a column of 8 outputs; a pixel whose
+    // fast value lies within the proven error bound of a threshold is redone exactly.
+    constexpr int HE = MODE == K1_FAST_HE2 ? 2 : HS;
+    constexpr int NT = 2 * HE + 1;
+    constexpr int RB = 8;                       // output rows per thread
+    for (int it = tid; it < (K1_TH / RB) * (K1_TW / 4); it += K1_THREADS) {
+      const int band = it / (K1_TW / 4), xq = it - band * (K1_TW / 4);
+      const int oyl0 = band * RB;
+      const int ox = x0 + 4 * xq;
+      float hsum[RB + 2 * HE][4], cv[RB][4];
+#pragma unroll
+      for (int ri = 0; ri < RB + 2 * HE; ++ri) {
+        const float* row = M + (oyl0 + K1_HS_MAX - HE + ri) * K1_MW + 4 * xq;
+        const float4 q0 = *reinterpret_cast<const float4*>(row);
+        const float4 q1 = *reinterpret_cast<const float4*>(row + 4);
+        const float4 q2 = *reinterpret_cast<const float4*>(row + 8);
+        const float r12[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float a = 0.0f;
+#pragma unroll
+          for (int t = 0; t < NT; ++t) a = __fmaf_rn(p.gx[t + (K1_HS_MAX - HE)], r12[K1_HS_MAX + j + t - HE], a);
+          hsum[ri][j] = a;
+          if (ri >= HE && ri < HE + RB) cv[ri - HE][j] = r12[K1_HS_MAX + j];
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        const int oy = y0 + oyl0 + r;
+        uint32_t nib = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float blur = 0.0f;
+#pragma unroll
+          for (int t = 0; t < NT; ++t) blur = __fmaf_rn(p.gx[t + (K1_HS_MAX - HE)], hsum[r + t][j], blur);
+          const float v = cv[r][j];
+          float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
+          const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
+          if (fabsf(sv - p.rg_min) <= eps || fabsf(sv - p.rg_max) <= eps) {
+            const float be = blur1_exact<HS>(M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX, p);
+            sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, be)));
+          }
+          if (ox + j < w && sv >= p.rg_min && sv <= p.rg_max) nib |= 1u << j;
+        }
+        uint32_t word = nib << (4 * (lane & 7));
+        word |= __shfl_xor_sync(0xffffffffu, word, 1);
+        word |= __shfl_xor_sync(0xffffffffu, word, 2);
+        word |= __shfl_xor_sync(0xffffffffu, word, 4);
+        if (p.predicate && (lane & 7) == 0 && oy < h) {
+          const int wi = (x0 >> 5) + (lane >> 3);
+          if (wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = word;
+        }
+        if (p.median && oy < h) {
+          const size_t rowoff = ((size_t)slice * h + oy) * w;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) if (ox + j < w) p.median[rowoff + ox + j] = cv[r][j];
+        }
+      }
+    }
+  }
 }
 
-template <int K, int HS>
-static cudaError_t launch_k1(const PreParams& p, cudaStream_t s) {
+template <int K, int HS, int MODE>
+static cudaError_t launch_k1m(const PreParams& p, cudaStream_t s) {
   constexpr int R = K / 2;
   const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4;
   const int grid = p.n * p.tiles_x * p.tiles_y;
-  k1_preprocess<K, HS><<<grid, K1_THREADS, smem, s>>>(p);
+  k1_preprocess<K, HS, MODE><<<grid, K1_THREADS, smem, s>>>(p);
   return cudaGetLastError();
+}
+
+template <int K, int HS>
+static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
+  if (mode == K1_FAST_HE2 && HS > 2) return launch_k1m<K, HS, (HS > 2 ? K1_FAST_HE2 : K1_FAST_FULL)>(p, s);
+  if (mode != K1_EXACT) return launch_k1m<K, HS, K1_FAST_FULL>(p, s);
+  return launch_k1m<K, HS, K1_EXACT>(p, s);
 }
 
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
-  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4;
-  return cudaFuncSetAttribute(k1_preprocess<K, HS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4);
+  cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e == cudaSuccess && HS > 2)
+    e = cudaFuncSetAttribute(k1_preprocess<K, HS, (HS > 2 ? K1_FAST_HE2 : K1_FAST_FULL)>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  return e;
 }
 
 #define NM03_K1_DISPATCH(FN, ...)                                                                   \
@@ -264,8 +356,8 @@ static cudaError_t config_k1() {
     default: return cudaErrorInvalidValue;                                                          \
   }
 
-cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, cudaStream_t s) {
-  NM03_K1_DISPATCH(launch_k1, p, s)
+cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, int mode, cudaStream_t s) {
+  NM03_K1_DISPATCH(launch_k1, p, mode, s)
 }
 
 // =================================================================================================

@@ -68,6 +68,67 @@ def test_preprocess_uint16(lib, ctx):
     _cmp_pre(lib, ctx, cm.phantom(128, 160, 0, 0, dtype=np.uint16))
 
 
+# ---- fast predicate mode (no sharpened plane requested): separable blur + exact band recompute ----
+def _oracle_pred(raw, **kw):
+    p = cm.oparams(**kw)
+    if raw.dtype == np.uint16:
+        p.input_unsigned = 1
+    f = cm.o_clip(cm.o_normalize(raw, p.norm_low, p.norm_high, p.norm_min, p.norm_max), p.clip_min, p.clip_max)
+    med = cm.o_median(f, p.median_window, p.border_mode)
+    sh = cm.o_sharpen(med, p.sharpen_gain, p.sharpen_sigma, p.sharpen_mask, p.border_mode, p.sharpen_fma)
+    return med, ((sh >= np.float32(p.rg_min)) & (sh <= np.float32(p.rg_max))).astype(np.uint8)
+
+
+def _cmp_fast(lib, ctx, raw, **kw):
+    h, w = raw.shape
+    med, pred = _oracle_pred(raw, **kw)
+    got = ctx.preprocess(raw, lib.default_params(**kw), want=("predicate",))
+    np.testing.assert_array_equal(lib.unpack_predicate(got["predicate"], w), pred)
+    got = ctx.preprocess(raw, lib.default_params(**kw), want=("median", "predicate"))
+    np.testing.assert_array_equal(lib.unpack_predicate(got["predicate"], w), pred)
+    np.testing.assert_array_equal(got["median"], med)
+
+
+@pytest.mark.parametrize("w,h", [(256, 256), (130, 67), (517, 203), (512, 512)])
+def test_fast_predicate_shapes(lib, ctx, w, h):
+    _cmp_fast(lib, ctx, cm.phantom(w, h, 2, 5))
+    _cmp_fast(lib, ctx, cm.phantom(w, h, 2, 6, kind="lowcontrast"))
+
+
+def test_fast_predicate_adversarial_thresholds(lib, ctx):
+    """Images whose sharpened values sit on / next to the two thresholds: the band logic must fall
+    back to the exact evaluation exactly where rounding decides the bit."""
+    rng = np.random.default_rng(7)
+    _cmp_fast(lib, ctx, np.full((120, 140), 1200, np.int16))            # flat at rg_min
+    _cmp_fast(lib, ctx, np.full((120, 140), 2050, np.int16))            # flat at rg_max
+    _cmp_fast(lib, ctx, rng.integers(1198, 1203, (150, 160)).astype(np.int16))
+    _cmp_fast(lib, ctx, rng.integers(2048, 2053, (150, 160)).astype(np.int16))
+    steps = np.repeat(np.repeat(rng.integers(1190, 1211, (10, 12)), 16, 0), 16, 1).astype(np.int16)  # flat patches
+    _cmp_fast(lib, ctx, steps)
+    _cmp_fast(lib, ctx, rng.integers(-32768, 32768, (140, 133)).astype(np.int16))
+    _cmp_fast(lib, ctx, rng.integers(0, 65536, (128, 160)).astype(np.uint16))
+
+
+@pytest.mark.parametrize("kw", [dict(sharpen_fma=1), dict(border_mode=1), dict(median_window=5, sharpen_mask=5),
+                                dict(sharpen_sigma=1.0), dict(sharpen_sigma=0.8, sharpen_mask=7, sharpen_gain=-1.5),
+                                dict(clip_min=-3.0, norm_low=-1.0, rg_min=-0.2, rg_max=0.1),
+                                dict(median_window=3, sharpen_mask=3, sharpen_sigma=0.4)])
+def test_fast_predicate_switches(lib, ctx, kw):
+    _cmp_fast(lib, ctx, cm.phantom(200, 150, 4, 1), **kw)
+    rng = np.random.default_rng(3)
+    _cmp_fast(lib, ctx, rng.integers(1150, 2100, (130, 131)).astype(np.int16), **kw)
+
+
+def test_fast_pipeline_masks_only(lib, ctx):
+    """Pipeline without the float planes takes the fast K1 mode; masks stay bit-exact."""
+    raws = np.stack([cm.phantom(512, 512, 8, i, kind="lowcontrast" if i == 3 else "default") for i in range(4)])
+    res = ctx.process_batch(raws, lib.default_params(erode_size=3), want=("dilated", "eroded", "rg_mask"))
+    for i in range(4):
+        rc, exp = cm.o_pipeline(raws[i], cm.oparams(erode_size=3))
+        for name in ("rg_mask", "dilated", "eroded"):
+            np.testing.assert_array_equal(res[name][i], exp[name], err_msg=f"slice {i} {name}")
+
+
 # ---- region growing --------------------------------------------------------------------------
 def _rg_image(w, h, seed):
     rng = np.random.default_rng(seed)
