@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnm03.so")
+LIB_PATH = os.environ.get("NM03_LIB", os.path.join(_HERE, "libnm03.so"))  # NM03_LIB: tuning builds
 
 # every symbol include/nm03.h declares
 EXPORTS = [

@@ -290,6 +290,63 @@ def run_design(R, k, off, maxlen, presort=True):
     return net, raw, outs
 
 
+def run_design_core(R, k, pair_off, blk_off, maxlen, presort=True):
+    """Design B: outputs are handled in adjacent pairs (i, i+1) that share a CORE of k-1 columns
+    [i+1, i+k).  The core is merged once from aligned blocks of columns (shared with the neighbouring
+    pairs) and pruned to the few ranks that can still be the median (8 of 42 for k=7); each output
+    then needs only one rank selection between the core and its one private column."""
+    net = Net()
+    ncol = R + k - 1
+    raw = net.inputs(ncol * k)
+    total, rank = k * k, (k * k + 1) // 2
+    cols = []
+    for c in range(ncol):
+        cols += sort_n(net, raw[c * k:(c + 1) * k]) if presort else raw[c * k:(c + 1) * k]
+    cache = {}
+
+    def block(x, ln):
+        if (x, ln) not in cache:
+            if ln == 1:
+                cache[(x, ln)] = prune(Part(cols[x * k:(x + 1) * k], k), total, rank)
+            else:
+                cache[(x, ln)] = merge_parts(net, block(x, ln // 2), block(x + ln // 2, ln // 2), total, rank)
+        return cache[(x, ln)]
+
+    cores = {}
+
+    def core(a, b):
+        if (a, b) not in cores:
+            parts = [block(x, ln) for x, ln in dyadic_blocks(a, b, blk_off, maxlen)]
+            while len(parts) > 1:
+                parts.sort(key=lambda p: p.size)
+                parts = parts[2:] + [merge_parts(net, parts[0], parts[1], total, rank)]
+            cores[(a, b)] = parts[0]
+        return cores[(a, b)]
+
+    outs = []
+    for i in range(R):
+        if (i - pair_off) % 2 == 0 and i + 1 < R:
+            c, single = core(i + 1, i + k), i            # first of a pair
+        elif (i - pair_off) % 2 == 1 and i - 1 >= 0:
+            c, single = core(i, i + k - 1), i + k - 1    # second of a pair
+        else:                                            # unpaired output at the edge of the run
+            c, single = core(i + 1, i + k), i
+        outs.append(select_parts(net, c, block(single, 1), total, rank))
+    return net, raw, outs
+
+
+def best_core_design(R, k):
+    best = None
+    for maxlen in (1, 2, 4, 8):
+        for blk_off in range(maxlen):
+            for pair_off in (0, 1):
+                net, raw, outs = run_design_core(R, k, pair_off, blk_off, maxlen)
+                n = net.count(outs)
+                if best is None or n < best[0]:
+                    best = (n, pair_off, blk_off, maxlen)
+    return best
+
+
 def best_run_design(R, k):
     best = None
     for maxlen in (1, 2, 4, 8):
@@ -315,7 +372,7 @@ def check_run(net, raw, outs, R, k, trials=3000):
     return True
 
 
-RUN = 4  # outputs per thread-run (packed registers: 8 pixels)
+RUN = 8  # outputs per thread-run (packed registers: 16 pixels)
 
 
 def emit(args):
@@ -325,14 +382,15 @@ def emit(args):
     print(f"// o[i], i < {RUN} = median of the k x k window made of columns i .. i+k-1.")
     print(f"#define NM03_MEDIAN_RUN {RUN}")
     for k in (3, 5, 7):
-        n, maxlen, off = best_run_design(RUN, k)
-        net, raw, outs = run_design(RUN, k, off, maxlen)
+        n, pair_off, blk_off, maxlen = best_core_design(RUN, k)
+        net, raw, outs = run_design_core(RUN, k, pair_off, blk_off, maxlen)
         assert check_run(net, raw, outs, RUN, k), f"k={k} failed verification"
         net.fuse3(outs)
         assert check_run(net, raw, outs, RUN, k), f"k={k} failed verification after 3-input fusion"
         n3 = net.count(outs)
         print(f"\n// k={k}: {n} two-input ops, {n3} instructions after min3/max3 fusion "
-              f"({n3 / (2.0 * RUN):.1f} per pixel); aligned groups <= {maxlen} columns at offset {off}")
+              f"({n3 / (2.0 * RUN):.1f} per pixel); shared-core design, pair offset {pair_off}, "
+              f"aligned blocks <= {maxlen} columns at offset {blk_off}")
         print(f"#define NM03_MEDIAN_RUN_{k}(v, o) do {{ \\")
         in_names = [f"(v)[{c}][{r}]" for c in range(RUN + k - 1) for r in range(k)]
         body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(RUN)], indent="  ", prefix=f"m{k}_")
@@ -342,6 +400,15 @@ def emit(args):
 
 
 def report(args):
+    for k in (3, 5, 7):
+        for R in (2, 4, 8, 16):
+            n, pair_off, blk_off, maxlen = best_core_design(R, k)
+            net, raw, outs = run_design_core(R, k, pair_off, blk_off, maxlen)
+            ok = check_run(net, raw, outs, R, k, trials=500)
+            net.fuse3(outs)
+            print(f"core design k={k} R={R}: {n} ops ({n / R:.1f}/output), {net.count(outs)} fused "
+                  f"({net.count(outs) / (2.0 * R):.1f} instr/pixel packed) pair_off={pair_off} "
+                  f"blocks<={maxlen}@{blk_off} verified={ok}")
     for k in (3, 5, 7):
         for R in (1, 2, 4, 8):
             n, maxlen, off = best_run_design(R, k)
@@ -356,7 +423,9 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--emit", action="store_true")
     ap.add_argument("--report", action="store_true")
+    ap.add_argument("--run", type=int, default=RUN, help="outputs per thread-run")
     a = ap.parse_args()
+    RUN = a.run
     if a.emit:
         emit(a)
     else:

@@ -37,6 +37,8 @@ int fail(int code, const char* fmt, ...) {
 
 constexpr int kSlots = 4;
 
+const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
+
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
 // predicate is needed (A/B measurements; results are identical by construction)
 const bool g_force_exact = [] { const char* e = getenv("NM03_FORCE_EXACT_SHARPEN"); return e && e[0] == '1'; }();
@@ -283,6 +285,10 @@ int pick_cluster(int n, int h, int wpr, int* rows_per) {
     if (c == nm03::SEG_MAX_CLUSTER) return fail(NM03_ERR_TOO_LARGE, "slice of %d rows x %d words exceeds cluster capacity", h, wpr);
   }
   while (c < nm03::SEG_MAX_CLUSTER && n * c * 2 <= 148 && (h + 2 * c - 1) / (2 * c) >= 32) c *= 2;
+  if (g_force_cluster > 0) {  // NM03_CLUSTER: tuning override (must still fit)
+    int cc = g_force_cluster;
+    if ((cc == 1 || cc == 2 || cc == 4 || cc == 8) && nm03::seg_smem_bytes((h + cc - 1) / cc, wpr) <= cap && (h + cc - 1) / cc >= nm03::SEG_HALO) c = cc;
+  }
   *rows_per = (h + c - 1) / c;
   return c;
 }

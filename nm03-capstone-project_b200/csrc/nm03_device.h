@@ -9,14 +9,24 @@ namespace nm03 {
 // ---- K1: fused normalise + clip + median + sharpen + range predicate --------------------------
 // Output tile of one CTA.  The median is needed on the tile plus the sharpen halo (HS_MAX each
 // side); raw samples on that plus the median radius.
+#ifndef NM03_K1_TH
+#define NM03_K1_TH 64
+#endif
+#ifndef NM03_K1_THREADS
+#define NM03_K1_THREADS 256
+#endif
+#ifndef NM03_K1_MIN_CTAS
+#define NM03_K1_MIN_CTAS 2
+#endif
 constexpr int K1_TW = 128;
-constexpr int K1_TH = 64;
+constexpr int K1_TH = NM03_K1_TH;
 constexpr int K1_HS_MAX = 4;                      // sharpen mask up to 9x9
 constexpr int K1_MW = K1_TW + 2 * K1_HS_MAX;      // 136 median columns
 constexpr int K1_MH = K1_TH + 2 * K1_HS_MAX;      // 72 median rows
 constexpr int K1_MHP = K1_MH / 2;                 // 36 packed median rows (row p and row p+36 share a register)
 constexpr int K1_PWS = 144;                       // packed raw tile row stride in words (>= 136 + 6, multiple of 4)
-constexpr int K1_THREADS = 256;
+constexpr int K1_THREADS = NM03_K1_THREADS;
+constexpr int K1_MIN_CTAS = NM03_K1_MIN_CTAS;                   // resident CTAs per SM the register budget is set for
 
 struct PreParams {
   const void* in;        // [n][h][w] int16 / uint16

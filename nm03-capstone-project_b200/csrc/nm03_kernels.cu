@@ -125,7 +125,7 @@ __device__ __noinline__ float blur1_exact(const float* __restrict__ Mc, const Pr
 }
 
 template <int K, int HS, int MODE>
-__global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_constant__ PreParams p) {
+__global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p) {
   constexpr int R = K / 2;
   constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
   constexpr int RW = K1_MW + 2 * R;        // raw columns actually needed
@@ -184,8 +184,11 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_preprocess(const __grid_cons
     }
     float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
     float* mhi = mlo + K1_MHP * K1_MW;
-    *reinterpret_cast<float4*>(mlo) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-    *reinterpret_cast<float4*>(mhi) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+#pragma unroll
+    for (int i = 0; i < NM03_MEDIAN_RUN; i += 4) {
+      *reinterpret_cast<float4*>(mlo + i) = make_float4(lo[i], lo[i + 1], lo[i + 2], lo[i + 3]);
+      *reinterpret_cast<float4*>(mhi + i) = make_float4(hi[i], hi[i + 1], hi[i + 2], hi[i + 3]);
+    }
   }
   __syncthreads();
 
@@ -387,11 +390,83 @@ __device__ __forceinline__ void store_word_u8(uint8_t* __restrict__ row, int x, 
   }
 }
 
-// funnel: bits of the row shifted so that pixel x+s lands on x (s in -31..31), zeros from outside
-__device__ __forceinline__ uint32_t shifted(uint32_t l, uint32_t c, uint32_t r, int s) {
-  if (s == 0) return c;
-  if (s > 0) return (c >> s) | (r << (32 - s));   // pixel x+s -> x
-  return (c << (-s)) | (l >> (32 + s));           // pixel x-|s| -> x
+// One sweep pass of the flood fill over the rows this CTA owns.  A thread owns one 32-pixel word
+// column over a segment of rows and walks it down, then up; the freshly computed word of the previous
+// row travels in a register, the other vertical neighbour and the two horizontal neighbour words are
+// read from shared memory as they are (chaotic relaxation of a monotone operator: any interleaving
+// converges to the same fixed point, and a pass without any change proves it has been reached).
+// MASKED = image-border pixels may be labelled but never act as sources (rg_border_expand = 0).
+template <bool CONN8, bool MASKED>
+__device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32_t* __restrict__ Pp,
+                                         const SegParams& p, int nrows, int y_begin, int tid) {
+  const int wpr = p.wpr;
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+  const int lastk = (p.w - 1) >> 5;
+  const uint32_t lastbit = 1u << ((p.w - 1) & 31);
+  int changed = 0;
+  const int nseg = (nrows + p.seg_rows - 1) / p.seg_rows;
+  for (int it = tid; it < nseg * wpr; it += SEG_THREADS) {
+    const int sgi = it / wpr, k = it - sgi * wpr;
+    const int ra = sgi * p.seg_rows, rb = min(nrows, ra + p.seg_rows);
+    const bool has_l = k > 0, has_r = k < wpr - 1;
+    uint32_t colmask = 0xffffffffu, lmask = 0xffffffffu, rmask = 0xffffffffu;  // source masks: own, left, right word
+    if (MASKED) {
+      if (k == 0) colmask &= ~1u;
+      if (k == lastk) colmask &= ~lastbit;
+      if (k - 1 == 0) lmask &= ~1u;
+      if (k - 1 == lastk) lmask &= ~lastbit;
+      if (k + 1 == lastk) rmask &= ~lastbit;
+    }
+    auto row_is_source = [&](int rr) { return !MASKED || (y_begin + rr > 0 && y_begin + rr < p.h - 1); };
+    // words k-1, k, k+1 of one mask row: c = raw centre word, s/l/r = the three words as SOURCES
+    struct Row3 { uint32_t c, s, l, r; };
+    auto load_row = [&](int rr) {
+      const uint32_t* row = MROW(rr);
+      Row3 t;
+      t.c = row[k];
+      t.l = has_l ? row[k - 1] & lmask : 0u;
+      t.r = has_r ? row[k + 1] & rmask : 0u;
+      t.s = t.c & colmask;
+      if (MASKED && !row_is_source(rr)) { t.s = 0u; t.l = 0u; t.r = 0u; }
+      return t;
+    };
+#pragma unroll 1
+    for (int dir = 0; dir < 2; ++dir) {
+      const int step = dir == 0 ? 1 : -1;
+      int r = dir == 0 ? ra : rb - 1;
+      // software pipeline: rows r-step (behind), r (here), r+step (ahead) live in registers and the
+      // row after that is fetched while this one is computed, so a step's critical path is ALU only
+      Row3 behind = load_row(r - step), here = load_row(r), ahead = load_row(r + step);
+      uint32_t pw = Pp[r * wpr + k];
+      for (int cnt = ra; cnt < rb; ++cnt, r += step) {
+        const Row3 next = load_row(r + 2 * step);   // rows up to +-2 outside the segment exist (halo >= 2)
+        const uint32_t pw_next = (cnt + 1 < rb) ? Pp[(r + step) * wpr + k] : 0u;
+        const uint32_t m = here.c;
+        uint32_t vs = behind.s | ahead.s;
+        if (CONN8) vs |= (vs << 1) | (vs >> 1) | ((behind.l | ahead.l) >> 31) | ((behind.r | ahead.r) << 31);
+        const uint32_t hz = (here.l >> 31) | (here.r << 31);
+        const uint32_t cand = m | ((vs | hz) & pw);
+        uint32_t nw;
+        const bool src_here = row_is_source(r);
+        if (MASKED) {
+          const uint32_t rowmask = src_here ? colmask : 0u;
+          const uint32_t f = hfill(cand & rowmask, pw & rowmask);
+          nw = m | f | (pw & ~rowmask & (cand | (f << 1) | (f >> 1)));
+        } else {
+          nw = hfill(cand, pw);
+        }
+        if (nw != m) { MROW(r)[k] = nw; changed = 1; }
+        behind = here;
+        behind.c = nw;
+        behind.s = (MASKED && !src_here) ? 0u : nw & colmask;
+        here = ahead;
+        ahead = next;
+        pw = pw_next;
+      }
+    }
+  }
+#undef MROW
+  return changed;
 }
 
 __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_constant__ SegParams p) {
@@ -401,10 +476,10 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   const int rank = C > 1 ? (int)cluster.block_rank() : 0;
   const int slice = blockIdx.x / C;
   const int tid = threadIdx.x;
-  // planes with SEG_HALO halo rows above and below: row index r (-HALO .. rows+HALO-1)
+  // planes: predicate rows owned by this CTA; mask rows with SEG_HALO halo rows above and below
   uint32_t* Pp = smem;                                   // [rows][wpr]
   uint32_t* Mm = smem + (size_t)rows * wpr;              // [rows + 2*HALO][wpr]
-  __shared__ int s_flag[2];
+  __shared__ int s_flag[3];                              // rotating "somebody changed" flags (see below)
 #define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
   const int y_begin = rank * rows;                       // first image row owned
   const int nrows = max(0, min(rows, p.h - y_begin));    // rows actually inside the image
@@ -414,10 +489,11 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
   for (int i = tid; i < rows * wpr; i += SEG_THREADS) {
     const int r = i / wpr, k = i - r * wpr;
-    uint32_t v = r < nrows ? gp[(size_t)(y_begin + r) * wpr + k] : 0u;
+    uint32_t v = r < nrows ? __ldg(gp + (size_t)(y_begin + r) * wpr + k) : 0u;
     if (k == wpr - 1) v &= lastmask;
     Pp[i] = v;
   }
+  if (tid < 3) s_flag[tid] = 0;
   __syncthreads();
 
   int passes = 0;
@@ -439,88 +515,43 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
         }
       }
     }
-    __syncthreads();
+    if (C > 1) cluster.sync();  // every CTA's planes and flags are initialised before anyone touches them
+    else __syncthreads();
 
     // ---- fill: sweep passes until nothing changes anywhere in the cluster --------------------
+    // Cluster protocol, one cluster.sync per pass: a CTA that changed something in pass q stores 1
+    // into flag[q % 3] of EVERY CTA (distributed shared memory); after the sync all CTAs read the same
+    // OR.  flag[(q+2) % 3] is cleared for later use — it is next written in pass q+2, which no CTA can
+    // reach before this CTA has passed the sync of pass q+1, i.e. after the clear.
     const bool masked = !p.border_expand && !p.host_mode;
-    const int nseg = (nrows + p.seg_rows - 1) / p.seg_rows;
-    for (;;) {
+    int hchg = 0;
+    for (int q = 0;; ++q) {
       ++passes;
-      int changed = 0;
-      for (int it = tid; it < nseg * wpr; it += SEG_THREADS) {
-        const int sgi = it / wpr, k = it - sgi * wpr;
-        const int ra = sgi * p.seg_rows, rb = min(nrows, ra + p.seg_rows);
-        // interior-column mask of this word (pixels allowed to expand)
-        uint32_t colmask = 0xffffffffu;
-        if (masked) {
-          if (k == 0) colmask &= ~1u;
-          if (k == (p.w - 1) >> 5) colmask &= ~(1u << ((p.w - 1) & 31));
-        }
-#pragma unroll 1
-        for (int dir = 0; dir < 2; ++dir) {
-          int r = dir == 0 ? ra : rb - 1;
-          const int step = dir == 0 ? 1 : -1;
-          for (int cnt = ra; cnt < rb; ++cnt, r += step) {
-            const int y = y_begin + r;
-            const int rs = r - step;  // source row of this sweep direction
-            const int ro = r + step;  // the other vertical neighbour
-            auto src_row = [&](int rr, int kk) -> uint32_t {
-              if (kk < 0 || kk >= wpr) return 0u;
-              uint32_t v = MROW(rr)[kk];
-              if (masked) {
-                const int yy = y_begin + rr;
-                if (yy <= 0 || yy >= p.h - 1) return 0u;
-                if (kk == 0) v &= ~1u;
-                if (kk == (p.w - 1) >> 5) v &= ~(1u << ((p.w - 1) & 31));
-              }
-              return v;
-            };
-            const uint32_t pw = Pp[r * wpr + k];
-            const uint32_t m = MROW(r)[k];
-            uint32_t vs = src_row(rs, k) | src_row(ro, k);
-            if (p.conn8) {
-              const uint32_t a = src_row(rs, k), b = src_row(ro, k);
-              vs |= (a << 1) | (a >> 1) | (b << 1) | (b >> 1);
-              vs |= (src_row(rs, k - 1) >> 31) | (src_row(rs, k + 1) << 31);
-              vs |= (src_row(ro, k - 1) >> 31) | (src_row(ro, k + 1) << 31);
-            }
-            const uint32_t hz = (src_row(r, k - 1) >> 31) | (src_row(r, k + 1) << 31);
-            const uint32_t cand = m | ((vs | hz) & pw);
-            uint32_t rowmask = colmask;
-            if (masked && (y <= 0 || y >= p.h - 1)) rowmask = 0u;
-            const uint32_t f = hfill(cand & rowmask, pw & rowmask);
-            const uint32_t bnd = pw & ~rowmask & (cand | (f << 1) | (f >> 1));
-            const uint32_t nw = m | f | bnd;
-            if (nw != m) { MROW(r)[k] = nw; changed = 1; }
-          }
-        }
-      }
+      int changed;
+      if (p.conn8) changed = masked ? fill_pass<true, true>(Mm, Pp, p, nrows, y_begin, tid) : fill_pass<true, false>(Mm, Pp, p, nrows, y_begin, tid);
+      else changed = masked ? fill_pass<false, true>(Mm, Pp, p, nrows, y_begin, tid) : fill_pass<false, false>(Mm, Pp, p, nrows, y_begin, tid);
+      changed = __syncthreads_or(changed | hchg);
       if (C == 1) {
-        if (!__syncthreads_or(changed)) break;
-      } else {
-        changed = __syncthreads_or(changed);
-        cluster.sync();  // every CTA finished its pass
-        // refresh the one halo row each side from the neighbouring CTAs; a change there is progress
-        int hchg = 0;
-        for (int k = tid; k < 2 * wpr; k += SEG_THREADS) {
-          const int side = k / wpr, kk = k - side * wpr;
-          const int nb = side == 0 ? rank - 1 : rank + 1;
-          if (nb < 0 || nb >= C) continue;
-          const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
-          const int rr = side == 0 ? rows - 1 : 0;          // neighbour's boundary row
-          const uint32_t v = remote[(size_t)(rr + SEG_HALO) * wpr + kk];
-          uint32_t* mine = MROW(side == 0 ? -1 : rows) + kk;
-          if (*mine != v) { *mine = v; hchg = 1; }
-        }
-        hchg = __syncthreads_or(hchg);
-        if (tid == 0) s_flag[0] = changed | hchg;
-        cluster.sync();  // flags written, halo reads done
-        int any = 0;
-        if (tid < C) any = *cluster.map_shared_rank(&s_flag[0], tid);
-        any = __syncthreads_or(any);
-        cluster.sync();  // everyone has read the flags before the next pass may rewrite them
-        if (!any) break;
+        if (!changed) break;
+        continue;
       }
+      if (changed && tid < C) *cluster.map_shared_rank(&s_flag[q % 3], tid) = 1;
+      cluster.sync();
+      const int any = s_flag[q % 3];
+      if (tid == 0) s_flag[(q + 2) % 3] = 0;
+      if (!any) break;
+      // refresh the one halo row each side from the neighbouring CTAs; a change there is progress
+      hchg = 0;
+      for (int k = tid; k < 2 * wpr; k += SEG_THREADS) {
+        const int side = k / wpr, kk = k - side * wpr;
+        const int nb = side == 0 ? rank - 1 : rank + 1;
+        if (nb < 0 || nb >= C) continue;
+        const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
+        const uint32_t v = remote[(size_t)((side == 0 ? rows - 1 : 0) + SEG_HALO) * wpr + kk];
+        uint32_t* mine = MROW(side == 0 ? -1 : rows) + kk;
+        if (*mine != v) { *mine = v; hchg = 1; }
+      }
+      __syncthreads();
     }
   } else {
     for (int i = tid; i < rows * wpr; i += SEG_THREADS) MROW(0)[i] = Pp[i];
@@ -529,9 +560,9 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   if (p.iterations && rank == 0 && tid == 0) p.iterations[slice] = passes;
 
   // ---- halo rows of the final mask for the structuring element --------------------------------
-  const int nmax = max(p.dil_n, p.ero_n);
-  if (C > 1 && nmax > 0) {
-    cluster.sync();
+  const int nmax = max(p.dilated ? p.dil_n : 0, p.eroded ? p.ero_n : 0);
+  if (C > 1) {
+    cluster.sync();  // all masks final (also orders the do_fill = 0 copy)
     for (int i = tid; i < 2 * nmax * wpr; i += SEG_THREADS) {
       const int side = i / (nmax * wpr), j = i - side * nmax * wpr;
       const int hr = j / wpr, kk = j - hr * wpr;
@@ -547,12 +578,13 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   }
 
   // ---- ImageCaster is the identity; dilation / erosion with the row-run form of the SE ---------
-  const bool vec = (p.w & 15) == 0;
+  const bool vec = (p.w & 15) == 0 && ((((size_t)p.dilated) | ((size_t)p.eroded) | ((size_t)p.rg_mask)) & 15) == 0;
   for (int i = tid; i < nrows * wpr; i += SEG_THREADS) {
     const int r = i / wpr, k = i - r * wpr;
     const int y = y_begin + r;
     const size_t rowoff = ((size_t)slice * p.h + y) * p.w;
     const uint32_t m = MROW(r)[k];
+    const bool has_l = k > 0, has_r = k < wpr - 1;
     if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
     if (p.dilated) {
       uint32_t acc = m;
@@ -562,9 +594,10 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
           const int yy = y + b;
           if (yy < 0 || yy >= p.h) continue;
           const uint32_t* row = MROW(r + b);
-          const uint32_t c = row[k], l = k > 0 ? row[k - 1] : 0u, rr = k < wpr - 1 ? row[k + 1] : 0u;
+          const uint32_t c = row[k], l = has_l ? row[k - 1] : 0u, rr = has_r ? row[k + 1] : 0u;
           const int hw = p.dil_hw[b + p.dil_n];
-          for (int s2 = -hw; s2 <= hw; ++s2) acc |= shifted(l, c, rr, s2);
+          acc |= c;
+          for (int s2 = 1; s2 <= hw; ++s2) acc |= __funnelshift_r(c, rr, s2) | __funnelshift_l(l, c, s2);
         }
       }
       store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
@@ -576,9 +609,10 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
           const int yy = y + b;
           if (yy < 0 || yy >= p.h) { acc = 0u; break; }
           const uint32_t* row = MROW(r + b);
-          const uint32_t c = row[k], l = k > 0 ? row[k - 1] : 0u, rr = k < wpr - 1 ? row[k + 1] : 0u;
+          const uint32_t c = row[k], l = has_l ? row[k - 1] : 0u, rr = has_r ? row[k + 1] : 0u;
           const int hw = p.ero_hw[b + p.ero_n];
-          for (int s2 = -hw; s2 <= hw; ++s2) acc &= shifted(l, c, rr, s2);
+          acc &= c;
+          for (int s2 = 1; s2 <= hw; ++s2) acc &= __funnelshift_r(c, rr, s2) & __funnelshift_l(l, c, s2);
         }
       }
       store_word_u8(p.eroded + rowoff, k * 32, p.w, acc, vec);

@@ -1,0 +1,34 @@
+#!/usr/bin/env python3
+"""Quick per-kernel timing of the device-resident pipeline (CUDA events inside the library).
+NM03_LIB selects the build.  usage: k_time.py [n_slices] [size] [steps]"""
+import importlib, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import bench
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 24
+steps = int(sys.argv[3]) if len(sys.argv) > 3 else 100
+nm03 = importlib.import_module("nm03-capstone-project_b200")
+dev = torch.device("cuda", 0)
+ctx = nm03.Context([0])
+d_in = bench.torch_series(torch, 24, dev, 1234)          # 24 series x 24 slices
+flat = d_in.reshape(-1, bench.H, bench.W)
+n_batches = flat.shape[0] // n
+d_out = torch.empty((n, bench.H, bench.W), dtype=torch.uint8, device=dev)
+o = nm03.Outputs(); o.dilated = d_out.data_ptr()
+it = torch.zeros(n, dtype=torch.int32, device=dev); o.rg_iterations = it.data_ptr()
+params = nm03.default_params()
+st = torch.cuda.Stream(device=dev)
+for i in range(5):
+    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, bench.W, bench.H, params, o, st.cuda_stream)
+torch.cuda.synchronize()
+ctx.profile_enable(True)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(st)
+for i in range(steps):
+    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, bench.W, bench.H, params, o, st.cuda_stream)
+e1.record(st)
+torch.cuda.synchronize()
+k1, k23, calls = ctx.profile_read()
+print(f"{os.path.basename(os.environ.get('NM03_LIB', 'libnm03.so')):28s} n={n:4d} step={e0.elapsed_time(e1)/steps*1e3:8.1f} us  "
+      f"k1={k1/calls*1e3:8.1f} us  k23={k23/calls*1e3:7.1f} us  -> {n*steps/(e0.elapsed_time(e1)*1e-3):10.0f} slices/s  "
+      f"fill passes max={int(it.max())} mean={float(it.float().mean()):.1f}")
