@@ -1,0 +1,242 @@
+// dicom.hpp — minimal DICOM Part-10 reader/writer for single-frame 16-bit monochrome slices.
+//
+// Replaces what the reference gets from FAST's DICOMFileImporter (DCMTK underneath) on the hot path:
+// `DICOMFileImporter::create(file)->setLoadSeries(false)->update()` yields ONE 2-D int16/uint16 image
+// (reference src/sequential/main_sequential.cpp:175-186, src/test/test_pipeline.cpp:33-51).
+// Supported: explicit and implicit VR little endian, uncompressed, BitsAllocated 16, one sample per
+// pixel, nested/undefined-length sequences are skipped.  Not supported (clear error): encapsulated
+// (compressed) transfer syntaxes, big endian, multi-frame.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <fstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace nm03 {
+namespace dicom {
+
+struct Slice {
+  int rows = 0, cols = 0;
+  int bits_allocated = 0;
+  int pixel_representation = 0;  // 0 = unsigned, 1 = two's complement
+  double rescale_slope = 1.0, rescale_intercept = 0.0;
+  int instance_number = 0;
+  std::vector<uint16_t> pixels;  // raw stored values, row-major
+};
+
+namespace detail {
+
+struct Cursor {
+  const uint8_t* p;
+  size_t n, off = 0;
+  bool has(size_t k) const { return off + k <= n; }
+  uint16_t u16() { if (!has(2)) throw std::runtime_error("DICOM: truncated file"); uint16_t v = (uint16_t)(p[off] | (p[off + 1] << 8)); off += 2; return v; }
+  uint32_t u32() { if (!has(4)) throw std::runtime_error("DICOM: truncated file"); uint32_t v = (uint32_t)p[off] | ((uint32_t)p[off + 1] << 8) | ((uint32_t)p[off + 2] << 16) | ((uint32_t)p[off + 3] << 24); off += 4; return v; }
+};
+
+inline bool long_vr(const char* vr) {
+  static const char* L[] = {"OB", "OW", "OF", "SQ", "UT", "UN", "OD", "OL", "UC", "UR", "OV", "SV", "UV"};
+  for (auto s : L) if (vr[0] == s[0] && vr[1] == s[1]) return true;
+  return false;
+}
+
+struct Element { uint16_t group, elem; char vr[3]; uint32_t len; size_t value_off; };
+
+// reads one element header; value is NOT consumed
+inline Element read_header(Cursor& c, bool explicit_vr) {
+  Element e{};
+  e.group = c.u16();
+  e.elem = c.u16();
+  e.vr[0] = e.vr[1] = '?'; e.vr[2] = 0;
+  if (e.group == 0xFFFE) {  // item / delimiters: always implicit form
+    e.len = c.u32();
+  } else if (explicit_vr) {
+    if (!c.has(2)) throw std::runtime_error("DICOM: truncated file");
+    e.vr[0] = (char)c.p[c.off]; e.vr[1] = (char)c.p[c.off + 1];
+    c.off += 2;
+    if (long_vr(e.vr)) { c.u16(); e.len = c.u32(); }
+    else e.len = c.u16();
+  } else {
+    e.len = c.u32();
+  }
+  e.value_off = c.off;
+  return e;
+}
+
+// skip a sequence / item of undefined length by walking its content
+inline void skip_undefined(Cursor& c, bool explicit_vr, bool is_item) {
+  for (;;) {
+    Element e = read_header(c, explicit_vr);
+    if (e.group == 0xFFFE && e.elem == 0xE0DD && !is_item) return;  // sequence delimitation
+    if (e.group == 0xFFFE && e.elem == 0xE00D && is_item) return;   // item delimitation
+    if (e.group == 0xFFFE && e.elem == 0xE000) {                     // item
+      if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, true);
+      else { if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated item"); c.off += e.len; }
+      continue;
+    }
+    if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, false);
+    else { if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated element"); c.off += e.len; }
+  }
+}
+
+inline std::string str_value(const Cursor& c, const Element& e) {
+  std::string s((const char*)c.p + e.value_off, e.len);
+  while (!s.empty() && (s.back() == ' ' || s.back() == '\0')) s.pop_back();
+  return s;
+}
+
+}  // namespace detail
+
+// Parse a Part-10 file image held in memory.
+inline Slice parse(const uint8_t* data, size_t size) {
+  using namespace detail;
+  Cursor c{data, size};
+  if (size < 132 || std::memcmp(data + 128, "DICM", 4) != 0) throw std::runtime_error("DICOM: missing DICM preamble");
+  c.off = 132;
+  std::string ts = "1.2.840.10008.1.2";  // default: implicit VR little endian
+  // file meta information: always explicit VR little endian, group 0002
+  while (c.has(8)) {
+    const size_t save = c.off;
+    Element e = read_header(c, true);
+    if (e.group != 0x0002) { c.off = save; break; }
+    if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated meta header");
+    if (e.elem == 0x0010) ts = str_value(c, e);
+    c.off += e.len;
+  }
+  bool explicit_vr;
+  if (ts == "1.2.840.10008.1.2") explicit_vr = false;
+  else if (ts == "1.2.840.10008.1.2.1") explicit_vr = true;
+  else throw std::runtime_error("DICOM: unsupported transfer syntax " + ts + " (only uncompressed little endian)");
+
+  Slice s;
+  int samples = 1, frames = 1;
+  bool have_pixels = false;
+  while (c.has(8)) {
+    Element e = read_header(c, explicit_vr);
+    if (e.len == 0xFFFFFFFFu) {
+      if (e.group == 0x7FE0 && e.elem == 0x0010) throw std::runtime_error("DICOM: encapsulated pixel data is not supported");
+      skip_undefined(c, explicit_vr, false);
+      continue;
+    }
+    if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated element");
+    const uint8_t* v = c.p + e.value_off;
+    auto us = [&]() { return e.len >= 2 ? (int)(v[0] | (v[1] << 8)) : 0; };
+    if (e.group == 0x0028) {
+      switch (e.elem) {
+        case 0x0002: samples = us(); break;
+        case 0x0008: frames = std::atoi(str_value(c, e).c_str()); break;
+        case 0x0010: s.rows = us(); break;
+        case 0x0011: s.cols = us(); break;
+        case 0x0100: s.bits_allocated = us(); break;
+        case 0x0103: s.pixel_representation = us(); break;
+        case 0x1052: s.rescale_intercept = std::atof(str_value(c, e).c_str()); break;
+        case 0x1053: s.rescale_slope = std::atof(str_value(c, e).c_str()); break;
+        default: break;
+      }
+    } else if (e.group == 0x0020 && e.elem == 0x0013) {
+      s.instance_number = std::atoi(str_value(c, e).c_str());
+    } else if (e.group == 0x7FE0 && e.elem == 0x0010) {
+      if (s.rows <= 0 || s.cols <= 0) throw std::runtime_error("DICOM: pixel data before image size");
+      if (s.bits_allocated != 16) throw std::runtime_error("DICOM: only 16-bit pixels are supported");
+      if (samples != 1) throw std::runtime_error("DICOM: only one sample per pixel is supported");
+      if (frames > 1) throw std::runtime_error("DICOM: multi-frame images are not supported");
+      const size_t need = (size_t)s.rows * s.cols * 2;
+      if (e.len < need) throw std::runtime_error("DICOM: pixel data shorter than rows*cols");
+      s.pixels.resize((size_t)s.rows * s.cols);
+      std::memcpy(s.pixels.data(), v, need);  // little endian host assumed (x86-64 / aarch64)
+      have_pixels = true;
+    }
+    c.off += e.len;
+    if (have_pixels) break;
+  }
+  if (!have_pixels) throw std::runtime_error("DICOM: no pixel data element");
+  return s;
+}
+
+inline std::vector<uint8_t> read_file(const std::string& path) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) throw std::runtime_error("cannot open " + path);
+  f.seekg(0, std::ios::end);
+  const std::streamsize n = f.tellg();
+  f.seekg(0);
+  std::vector<uint8_t> buf((size_t)n);
+  if (n > 0 && !f.read((char*)buf.data(), n)) throw std::runtime_error("cannot read " + path);
+  return buf;
+}
+
+inline Slice load(const std::string& path) {
+  const std::vector<uint8_t> buf = read_file(path);
+  return parse(buf.data(), buf.size());
+}
+
+// ---- writer (synthetic inputs: "identical synthetic DICOM inputs") -------------------
+namespace detail {
+struct Out {
+  std::vector<uint8_t> b;
+  void u16(uint16_t v) { b.push_back((uint8_t)v); b.push_back((uint8_t)(v >> 8)); }
+  void u32(uint32_t v) { for (int i = 0; i < 4; ++i) b.push_back((uint8_t)(v >> (8 * i))); }
+  void bytes(const void* p, size_t n) { const uint8_t* q = (const uint8_t*)p; b.insert(b.end(), q, q + n); }
+  void elem(bool explicit_vr, uint16_t g, uint16_t e, const char* vr, const void* val, uint32_t len) {
+    u16(g); u16(e);
+    if (explicit_vr) {
+      b.push_back((uint8_t)vr[0]); b.push_back((uint8_t)vr[1]);
+      if (long_vr(vr)) { u16(0); u32(len); } else u16((uint16_t)len);
+    } else {
+      u32(len);
+    }
+    bytes(val, len);
+  }
+  void str(bool ex, uint16_t g, uint16_t e, const char* vr, std::string s, char pad = ' ') {
+    if (s.size() & 1) s.push_back(pad);
+    elem(ex, g, e, vr, s.data(), (uint32_t)s.size());
+  }
+  void us(bool ex, uint16_t g, uint16_t e, uint16_t v) { uint8_t t[2] = {(uint8_t)v, (uint8_t)(v >> 8)}; elem(ex, g, e, "US", t, 2); }
+};
+}  // namespace detail
+
+inline std::vector<uint8_t> encode(const uint16_t* pixels, int cols, int rows, bool is_signed, int instance_number,
+                                   bool explicit_vr = true) {
+  using detail::Out;
+  const std::string ts = explicit_vr ? "1.2.840.10008.1.2.1" : "1.2.840.10008.1.2";
+  Out meta;
+  const uint8_t ver[2] = {0, 1};
+  meta.elem(true, 0x0002, 0x0001, "OB", ver, 2);
+  meta.str(true, 0x0002, 0x0002, "UI", "1.2.840.10008.5.1.4.1.1.4", '\0');  // MR Image Storage
+  meta.str(true, 0x0002, 0x0003, "UI", "1.2.826.0.1.3680043.9.7433.1." + std::to_string(instance_number), '\0');
+  meta.str(true, 0x0002, 0x0010, "UI", ts, '\0');
+  meta.str(true, 0x0002, 0x0012, "UI", "1.2.826.0.1.3680043.9.7433.0.1", '\0');
+  Out o;
+  o.b.assign(128, 0);
+  o.bytes("DICM", 4);
+  const uint32_t glen = (uint32_t)meta.b.size();
+  uint8_t gl[4] = {(uint8_t)glen, (uint8_t)(glen >> 8), (uint8_t)(glen >> 16), (uint8_t)(glen >> 24)};
+  o.elem(true, 0x0002, 0x0000, "UL", gl, 4);
+  o.bytes(meta.b.data(), meta.b.size());
+  const bool ex = explicit_vr;
+  o.str(ex, 0x0008, 0x0060, "CS", "MR");
+  o.str(ex, 0x0020, 0x0013, "IS", std::to_string(instance_number));
+  o.us(ex, 0x0028, 0x0002, 1);
+  o.str(ex, 0x0028, 0x0004, "CS", "MONOCHROME2");
+  o.us(ex, 0x0028, 0x0010, (uint16_t)rows);
+  o.us(ex, 0x0028, 0x0011, (uint16_t)cols);
+  o.us(ex, 0x0028, 0x0100, 16);
+  o.us(ex, 0x0028, 0x0101, 16);
+  o.us(ex, 0x0028, 0x0102, 15);
+  o.us(ex, 0x0028, 0x0103, is_signed ? 1 : 0);
+  o.str(ex, 0x0028, 0x1052, "DS", "0");
+  o.str(ex, 0x0028, 0x1053, "DS", "1");
+  o.elem(ex, 0x7FE0, 0x0010, "OW", pixels, (uint32_t)((size_t)rows * cols * 2));
+  return o.b;
+}
+
+inline void save(const std::string& path, const uint16_t* pixels, int cols, int rows, bool is_signed, int instance_number,
+                 bool explicit_vr = true) {
+  const std::vector<uint8_t> b = encode(pixels, cols, rows, is_signed, instance_number, explicit_vr);
+  std::ofstream f(path, std::ios::binary);
+  if (!f || !f.write((const char*)b.data(), (std::streamsize)b.size())) throw std::runtime_error("cannot write " + path);
+}
+
+}  // namespace dicom
+}  // namespace nm03

@@ -1,0 +1,596 @@
+// nm03.hpp — FAST-shaped C++17 shim over the C ABI (include/nm03.h).
+//
+// The reference drives FAST through `T::create(..)->connect(..)->update()` and
+// `getOutputData<Image>(0)` (src/sequential/main_sequential.cpp:175-262,
+// src/parallel/main_parallel.cpp:78-210, src/test/test_pipeline.cpp:33-177).  This header declares
+// classes with those names, members and error behaviour so that the body of processSingleImage()
+// compiles unchanged (`namespace fast = nm03;`, see host/compat/FAST/FAST_directives.hpp), while the
+// arithmetic runs in libnm03.so on the GPU.
+//
+// Evaluation is lazy and fused: update() on the preprocessing / segmentation stages only records the
+// request; Dilation::update() / Erosion::update() (or the first getOutputData() that needs pixels)
+// recognises the reference's chain  importer -> normalise -> clip -> median -> sharpen -> region
+// growing -> caster -> dilation|erosion  and issues ONE nm03_process_batch call for the slice.
+// Anything FAST would throw surfaces as nm03::Exception from that call, inside the same try block
+// the reference uses (main_sequential.cpp:267, main_parallel.cpp:163).
+//
+// Rendering (ImageRenderer / SegmentationRenderer / RenderToImage) is FAST's OpenGL path in the
+// reference; a graphics stack is unavailable on this box, so it is restated on the CPU (window/level,
+// label overlay, aspect-fit into the canvas).  Pixel parity with FAST's renderer is not claimed.
+#pragma once
+#include <nm03.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <exception>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "dicom.hpp"
+#include "jpeg.hpp"
+
+namespace nm03 {
+
+class Exception : public std::exception {
+  std::string msg_;
+ public:
+  explicit Exception(std::string m) : msg_(std::move(m)) {}
+  const char* what() const noexcept override { return msg_.c_str(); }
+};
+
+struct Vector3i {
+  int v[3];
+  Vector3i(int x = 0, int y = 0, int z = 0) : v{x, y, z} {}
+  int x() const { return v[0]; }
+  int y() const { return v[1]; }
+  int z() const { return v[2]; }
+  int operator[](int i) const { return v[i]; }
+};
+
+enum DataType { TYPE_FLOAT, TYPE_UINT8, TYPE_INT8, TYPE_UINT16, TYPE_INT16 };
+
+struct Color {
+  float r, g, b;
+  static Color White() { return {1, 1, 1}; }
+  static Color Black() { return {0, 0, 0}; }
+  static Color Red() { return {1, 0, 0}; }
+  static Color Green() { return {0, 1, 0}; }
+};
+using LabelColors = std::map<int, Color>;
+
+struct Config {
+  // FAST's Config::getTestDataPath() (main_sequential.cpp:83): here the NM03_TEST_DATA_PATH variable
+  static std::string getTestDataPath() {
+    const char* e = std::getenv("NM03_TEST_DATA_PATH");
+    std::string p = e ? e : "./data/";
+    if (!p.empty() && p.back() != '/') p.push_back('/');
+    return p;
+  }
+};
+
+struct Reporter {  // logging configuration is a no-op (main_sequential.cpp:310-315)
+  enum Type { INFO, WARNING, ERROR };
+  enum Method { NONE, COUT };
+  static void setGlobalReportMethod(Type, Method) {}
+};
+
+struct QApplication {  // main_parallel.cpp:391 needs one only for FAST's GL context
+  QApplication(int&, char**) {}
+};
+
+// ---- data objects ----------------------------------------------------------------------------
+class Image {
+ public:
+  Image(int w, int h, DataType t, int channels = 1) : w_(w), h_(h), c_(channels), type_(t) {
+    bytes_.resize((size_t)w * h * channels * elemSize(t));
+  }
+  int getWidth() const { return w_; }
+  int getHeight() const { return h_; }
+  int getNrOfChannels() const { return c_; }
+  DataType getDataType() const { return type_; }
+  void* data() { return bytes_.data(); }
+  const void* data() const { return bytes_.data(); }
+  template <class T> T* as() { return reinterpret_cast<T*>(bytes_.data()); }
+  template <class T> const T* as() const { return reinterpret_cast<const T*>(bytes_.data()); }
+  static size_t elemSize(DataType t) { return t == TYPE_FLOAT ? 4 : (t == TYPE_UINT8 || t == TYPE_INT8) ? 1 : 2; }
+ private:
+  int w_, h_, c_;
+  DataType type_;
+  std::vector<uint8_t> bytes_;
+};
+using Segmentation = Image;
+
+// ---- runtime: one context over the visible GPUs, slices assigned round-robin per host thread ----
+class Runtime {
+ public:
+  static Runtime& get() {
+    static Runtime rt;
+    return rt;
+  }
+  nm03_ctx* ctx() const { return ctx_; }
+  int gpuForThisThread() {
+    thread_local int g = -1;
+    if (g < 0) g = next_.fetch_add(1) % ngpus_;
+    return g;
+  }
+  static void check(int rc) {
+    if (rc != NM03_OK) throw Exception(nm03_last_error());
+  }
+ private:
+  Runtime() {
+    std::vector<int> ids;
+    if (const char* e = std::getenv("NM03_GPUS")) {
+      for (const char* p = e; *p;) { ids.push_back(std::atoi(p)); while (*p && *p != ',') ++p; if (*p) ++p; }
+    }
+    int rc = nm03_init(ids.empty() ? nullptr : ids.data(), (int)ids.size(), &ctx_);
+    if (rc != NM03_OK) throw Exception(nm03_last_error());
+    ngpus_ = nm03_gpu_count(ctx_);
+  }
+  ~Runtime() { nm03_shutdown(ctx_); }
+  nm03_ctx* ctx_ = nullptr;
+  int ngpus_ = 1;
+  std::atomic<int> next_{0};
+};
+
+// ---- process objects ---------------------------------------------------------------------------
+class ProcessObject : public std::enable_shared_from_this<ProcessObject> {
+ public:
+  enum Kind { IMPORTER, NORMALIZE, CLIP, MEDIAN, SHARPEN, REGION_GROW, CASTER, DILATE, ERODE, RENDERER, RENDER_TO_IMAGE, EXPORTER, OTHER };
+  virtual ~ProcessObject() = default;
+  virtual void update() {}
+  template <class T = Image>
+  std::shared_ptr<T> getOutputData(int /*port*/ = 0) {
+    if (!output_) evaluate();
+    return output_;
+  }
+  Kind kind() const { return kind_; }
+  std::shared_ptr<ProcessObject> parent() const { return parent_; }
+  // input image of this object: the connected data object, or the parent's output
+  std::shared_ptr<Image> inputImage() {
+    if (inputData_) return inputData_;
+    if (!parent_) throw Exception("process object has no input connection");
+    return parent_->getOutputData<Image>(0);
+  }
+  bool hasOutput() const { return (bool)output_; }
+  void setOutput(std::shared_ptr<Image> img) { output_ = std::move(img); }
+ protected:
+  explicit ProcessObject(Kind k) : kind_(k) {}
+  virtual void evaluate() { throw Exception("this process object produces no image"); }
+  void connectParent(std::shared_ptr<ProcessObject> p) { parent_ = std::move(p); output_.reset(); }
+  void connectData(std::shared_ptr<Image> d) { inputData_ = std::move(d); output_.reset(); }
+  Kind kind_;
+  std::shared_ptr<ProcessObject> parent_;
+  std::shared_ptr<Image> inputData_;
+  std::shared_ptr<Image> output_;
+};
+
+// typed create()/connect() as FAST's FAST_PROCESS_OBJECT/FAST_CONSTRUCTOR macros generate them
+template <class D>
+class Typed : public ProcessObject {
+ public:
+  template <class... A>
+  static std::shared_ptr<D> create(A&&... a) { return std::shared_ptr<D>(new D(std::forward<A>(a)...)); }
+  std::shared_ptr<D> connect(std::shared_ptr<ProcessObject> p) {
+    connectParent(std::move(p));
+    return self();
+  }
+  std::shared_ptr<D> connect(std::shared_ptr<Image> d) {
+    connectData(std::move(d));
+    return self();
+  }
+  std::shared_ptr<D> addInputData(std::shared_ptr<Image> d) { return connect(std::move(d)); }
+ protected:
+  explicit Typed(Kind k) : ProcessObject(k) {}
+  std::shared_ptr<D> self() { return std::static_pointer_cast<D>(shared_from_this()); }
+};
+
+class DICOMFileImporter : public Typed<DICOMFileImporter> {
+ public:
+  void setLoadSeries(bool) {}  // a single 2-D slice is all this importer ever loads (test_pipeline.cpp:38-42)
+  void update() override { if (!output_) evaluate(); }
+  bool isUnsigned() const { return unsigned_; }
+ protected:
+  friend class Typed<DICOMFileImporter>;
+  explicit DICOMFileImporter(std::string file) : Typed(IMPORTER), file_(std::move(file)) {}
+  void evaluate() override {
+    try {
+      dicom::Slice s = dicom::load(file_);
+      unsigned_ = s.pixel_representation == 0;
+      auto img = std::make_shared<Image>(s.cols, s.rows, unsigned_ ? TYPE_UINT16 : TYPE_INT16);
+      std::memcpy(img->data(), s.pixels.data(), s.pixels.size() * 2);
+      output_ = img;
+    } catch (const std::exception& e) {
+      throw Exception(e.what());
+    }
+  }
+  std::string file_;
+  bool unsigned_ = false;
+};
+
+class IntensityNormalization : public Typed<IntensityNormalization> {
+ public:
+  float low, high, mn, mx;
+ protected:
+  friend class Typed<IntensityNormalization>;
+  IntensityNormalization(float valueLow = 0.0f, float valueHigh = 1.0f, float minIntensity = NAN, float maxIntensity = NAN)
+      : Typed(NORMALIZE), low(valueLow), high(valueHigh), mn(minIntensity), mx(maxIntensity) {}
+  void evaluate() override { throw Exception("IntensityNormalization output is only available fused with median + sharpen"); }
+};
+
+class IntensityClipping : public Typed<IntensityClipping> {
+ public:
+  float lo, hi;
+ protected:
+  friend class Typed<IntensityClipping>;
+  IntensityClipping(float minValue = 0.0f, float maxValue = 4000.0f) : Typed(CLIP), lo(minValue), hi(maxValue) {}
+  void evaluate() override { throw Exception("IntensityClipping output is only available fused with median + sharpen"); }
+};
+
+struct Chain;  // forward
+
+class VectorMedianFilter : public Typed<VectorMedianFilter> {
+ public:
+  int window;
+ protected:
+  friend class Typed<VectorMedianFilter>;
+  explicit VectorMedianFilter(int size = 3) : Typed(MEDIAN), window(size) {}
+  void evaluate() override;
+};
+
+class ImageSharpening : public Typed<ImageSharpening> {
+ public:
+  float gain, sigma;
+  int mask;
+ protected:
+  friend class Typed<ImageSharpening>;
+  ImageSharpening(float g = 1.0f, float stdDev = 0.5f, int maskSize = 3) : Typed(SHARPEN), gain(g), sigma(stdDev), mask(maskSize) {}
+  void evaluate() override;
+};
+
+class SeededRegionGrowing : public Typed<SeededRegionGrowing> {
+ public:
+  float lo, hi;
+  std::vector<int> seeds;  // x,y pairs
+  void addSeedPoint(int x, int y) { seeds.push_back(x); seeds.push_back(y); output_.reset(); }
+  void addSeedPoint(Vector3i p) { addSeedPoint(p.x(), p.y()); }
+ protected:
+  friend class Typed<SeededRegionGrowing>;
+  SeededRegionGrowing(float intensityMinimum, float intensityMaximum, std::vector<Vector3i> seedPoints = {})
+      : Typed(REGION_GROW), lo(intensityMinimum), hi(intensityMaximum) {
+    for (auto& s : seedPoints) addSeedPoint(s);
+  }
+  void evaluate() override;
+};
+
+class ImageCaster : public Typed<ImageCaster> {
+ public:
+  DataType type;
+  float scale;
+ protected:
+  friend class Typed<ImageCaster>;
+  explicit ImageCaster(DataType outputType, float scaleFactor = 1.0f) : Typed(CASTER), type(outputType), scale(scaleFactor) {}
+  void evaluate() override {
+    auto in = inputImage();
+    if (type != TYPE_UINT8 || in->getDataType() != TYPE_UINT8)
+      throw Exception("ImageCaster: only the uint8 -> uint8 cast of the reference pipeline is implemented");
+    output_ = in;  // identity on a {0,1} segmentation (main_sequential.cpp:246-248)
+  }
+};
+
+class Morphology : public ProcessObject {
+ public:
+  int size;
+  void update() override { if (!output_) evaluate(); }
+ protected:
+  Morphology(Kind k, int s) : ProcessObject(k), size(s) {}
+  void evaluate() override;
+};
+
+class Dilation : public Morphology {
+ public:
+  static std::shared_ptr<Dilation> create(int size = 3) { return std::shared_ptr<Dilation>(new Dilation(size)); }
+  std::shared_ptr<Dilation> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return std::static_pointer_cast<Dilation>(shared_from_this()); }
+ private:
+  explicit Dilation(int s) : Morphology(DILATE, s) {}
+};
+
+class Erosion : public Morphology {
+ public:
+  static std::shared_ptr<Erosion> create(int size = 3) { return std::shared_ptr<Erosion>(new Erosion(size)); }
+  std::shared_ptr<Erosion> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return std::static_pointer_cast<Erosion>(shared_from_this()); }
+ private:
+  explicit Erosion(int s) : Morphology(ERODE, s) {}
+};
+
+// ---- chain recognition + fused evaluation ---------------------------------------------------------
+struct Chain {
+  std::shared_ptr<Image> raw;
+  IntensityNormalization* norm = nullptr;
+  IntensityClipping* clip = nullptr;
+  VectorMedianFilter* median = nullptr;
+  ImageSharpening* sharpen = nullptr;
+  SeededRegionGrowing* rg = nullptr;
+  nm03_params params;
+
+  // walk up from `top` (a MEDIAN, SHARPEN or REGION_GROW node)
+  static Chain fromNode(ProcessObject* top) {
+    Chain c;
+    nm03_default_params(&c.params);
+    ProcessObject* n = top;
+    if (n->kind() == ProcessObject::REGION_GROW) { c.rg = static_cast<SeededRegionGrowing*>(n); n = n->parent().get(); }
+    if (n && n->kind() == ProcessObject::SHARPEN) { c.sharpen = static_cast<ImageSharpening*>(n); n = n->parent().get(); }
+    if (n && n->kind() == ProcessObject::MEDIAN) { c.median = static_cast<VectorMedianFilter*>(n); n = n->parent().get(); }
+    if (n && n->kind() == ProcessObject::CLIP) { c.clip = static_cast<IntensityClipping*>(n); n = n->parent().get(); }
+    if (n && n->kind() == ProcessObject::NORMALIZE) { c.norm = static_cast<IntensityNormalization*>(n); n = n->parent().get(); }
+    if (!n || !c.norm || !c.clip || !c.median)
+      throw Exception("unsupported operator chain: expected importer -> IntensityNormalization -> IntensityClipping -> "
+                      "VectorMedianFilter -> ImageSharpening [-> SeededRegionGrowing]");
+    if (std::isnan(c.norm->mn) || std::isnan(c.norm->mx))
+      throw Exception("IntensityNormalization without explicit min/max intensity is not implemented");
+    c.raw = n->getOutputData<Image>(0);
+    if (!c.raw) throw Exception("Failed to get imported image");
+    if (c.raw->getDataType() != TYPE_INT16 && c.raw->getDataType() != TYPE_UINT16)
+      throw Exception("pipeline input must be a 16-bit image");
+    nm03_params& p = c.params;
+    p.norm_low = c.norm->low; p.norm_high = c.norm->high; p.norm_min = c.norm->mn; p.norm_max = c.norm->mx;
+    p.clip_min = c.clip->lo; p.clip_max = c.clip->hi;
+    p.median_window = c.median->window;
+    if (c.sharpen) { p.sharpen_gain = c.sharpen->gain; p.sharpen_sigma = c.sharpen->sigma; p.sharpen_mask = c.sharpen->mask; }
+    if (c.rg) { p.rg_min = c.rg->lo; p.rg_max = c.rg->hi; }
+    p.input_unsigned = c.raw->getDataType() == TYPE_UINT16;
+    return c;
+  }
+
+  void preprocess(bool want_sharpened) {
+    Runtime& rt = Runtime::get();
+    const int w = raw->getWidth(), h = raw->getHeight();
+    auto med = std::make_shared<Image>(w, h, TYPE_FLOAT);
+    std::shared_ptr<Image> sh = want_sharpened ? std::make_shared<Image>(w, h, TYPE_FLOAT) : nullptr;
+    Runtime::check(nm03_preprocess(rt.ctx(), rt.gpuForThisThread(), raw->data(), w, h, &params, med->as<float>(),
+                                   sh ? sh->as<float>() : nullptr, nullptr));
+    median->setOutput(med);
+    if (sh) sharpen->setOutput(sh);
+  }
+
+  // whole pipeline for the slice in one call; morph_size 0 = stop after region growing
+  void pipeline(int dilate_size, std::shared_ptr<Image>* dilated, int erode_size, std::shared_ptr<Image>* eroded) {
+    Runtime& rt = Runtime::get();
+    const int w = raw->getWidth(), h = raw->getHeight();
+    if (!sharpen) throw Exception("SeededRegionGrowing must be connected to ImageSharpening in the fused pipeline");
+    auto mask = std::make_shared<Image>(w, h, TYPE_UINT8);
+    nm03_outputs out = {};
+    out.rg_mask = mask->as<uint8_t>();
+    // FAST validates Dilation/Erosion sizes even when only one of them is requested here
+    params.dilate_size = dilate_size > 0 ? dilate_size : 3;
+    params.erode_size = erode_size;
+    if (dilate_size > 0) { *dilated = std::make_shared<Image>(w, h, TYPE_UINT8); out.dilated = (*dilated)->as<uint8_t>(); }
+    if (erode_size > 0) { *eroded = std::make_shared<Image>(w, h, TYPE_UINT8); out.eroded = (*eroded)->as<uint8_t>(); }
+    Runtime::check(nm03_process_batch(rt.ctx(), rt.gpuForThisThread(), raw->data(), 1, w, h, &params,
+                                      rg->seeds.empty() ? nullptr : rg->seeds.data(), (int)rg->seeds.size() / 2, &out, nullptr));
+    rg->setOutput(mask);
+  }
+};
+
+inline void VectorMedianFilter::evaluate() {
+  Chain c = Chain::fromNode(this);
+  c.preprocess(false);
+}
+
+inline void ImageSharpening::evaluate() {
+  Chain c = Chain::fromNode(this);
+  c.preprocess(true);
+}
+
+inline void SeededRegionGrowing::evaluate() {
+  if (seeds.empty()) throw Exception("SeededRegionGrowing: no seed points");
+  if (parent_ && parent_->hasOutput()) {  // stage-by-stage: the input image already exists
+    auto in = parent_->getOutputData<Image>(0);
+    if (in->getDataType() != TYPE_FLOAT) throw Exception("SeededRegionGrowing: only float input is implemented");
+    nm03_params p;
+    nm03_default_params(&p);
+    p.rg_min = lo; p.rg_max = hi;
+    auto mask = std::make_shared<Image>(in->getWidth(), in->getHeight(), TYPE_UINT8);
+    Runtime& rt = Runtime::get();
+    Runtime::check(nm03_region_grow(rt.ctx(), rt.gpuForThisThread(), in->as<float>(), in->getWidth(), in->getHeight(), &p,
+                                    seeds.data(), (int)seeds.size() / 2, mask->as<uint8_t>(), nullptr));
+    output_ = mask;
+    return;
+  }
+  Chain c = Chain::fromNode(this);
+  c.pipeline(0, nullptr, 0, nullptr);
+}
+
+inline void Morphology::evaluate() {
+  if (!parent_) throw Exception("morphology operator has no input connection");
+  // the reference's chain: (Dilation|Erosion) <- ImageCaster <- SeededRegionGrowing <- ... nothing computed yet
+  ProcessObject* n = parent_.get();
+  ProcessObject* caster = nullptr;
+  if (n->kind() == CASTER) { caster = n; n = n->parent().get(); }
+  if (n && n->kind() == REGION_GROW && !n->hasOutput() && !(n->parent() && n->parent()->hasOutput())) {
+    Chain c = Chain::fromNode(n);
+    std::shared_ptr<Image> res;
+    if (kind_ == DILATE) c.pipeline(size, &res, 0, nullptr);
+    else {
+      if (size <= 2 || (size & 1) == 0) throw Exception("morphology size must be odd and > 2");
+      c.pipeline(0, nullptr, size, &res);
+    }
+    if (caster) caster->setOutput(n->getOutputData<Image>(0));
+    output_ = res;
+    return;
+  }
+  auto in = parent_->getOutputData<Image>(0);
+  if (in->getDataType() != TYPE_UINT8) throw Exception("Dilation/Erosion need a TYPE_UINT8 image (cast it first)");
+  auto out = std::make_shared<Image>(in->getWidth(), in->getHeight(), TYPE_UINT8);
+  Runtime& rt = Runtime::get();
+  Runtime::check(nm03_morphology(rt.ctx(), rt.gpuForThisThread(), in->as<uint8_t>(), in->getWidth(), in->getHeight(), size,
+                                 NM03_SE_DISC, kind_ == DILATE ? NM03_MORPH_DILATE : NM03_MORPH_ERODE, out->as<uint8_t>()));
+  output_ = out;
+}
+
+// ---- rendering + export (CPU restatement of FAST's GL renderers; host side, e2e figure only) ------
+class Renderer : public ProcessObject {
+ public:
+  // paint this renderer's input into an RGB canvas (aspect-fit, centred)
+  virtual void paint(uint8_t* rgb, int cw, int ch) = 0;
+ protected:
+  Renderer() : ProcessObject(RENDERER) {}
+  struct Fit { float scale; float ox, oy; };
+  static Fit fit(int iw, int ih, int cw, int ch) {
+    const float s = std::min((float)cw / iw, (float)ch / ih);
+    return {s, (cw - iw * s) * 0.5f, (ch - ih * s) * 0.5f};
+  }
+};
+
+class ImageRenderer : public Renderer {
+ public:
+  static std::shared_ptr<ImageRenderer> create() { return std::shared_ptr<ImageRenderer>(new ImageRenderer()); }
+  std::shared_ptr<ImageRenderer> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return me(); }
+  std::shared_ptr<ImageRenderer> addInputData(std::shared_ptr<Image> d) { connectData(std::move(d)); return me(); }
+  void paint(uint8_t* rgb, int cw, int ch) override {
+    auto img = inputImage();
+    const int w = img->getWidth(), h = img->getHeight();
+    auto at = [&](int x, int y) -> float {
+      const size_t i = (size_t)y * w + x;
+      switch (img->getDataType()) {
+        case TYPE_FLOAT: return img->as<float>()[i];
+        case TYPE_UINT8: return img->as<uint8_t>()[i];
+        case TYPE_UINT16: return img->as<uint16_t>()[i];
+        default: return img->as<int16_t>()[i];
+      }
+    };
+    float lo = at(0, 0), hi = lo;  // window = full intensity range of the image, level = its centre
+    for (int y = 0; y < h; ++y) for (int x = 0; x < w; ++x) { const float v = at(x, y); lo = std::min(lo, v); hi = std::max(hi, v); }
+    const float inv = hi > lo ? 255.0f / (hi - lo) : 0.0f;
+    const Fit f = fit(w, h, cw, ch);
+    for (int cy = 0; cy < ch; ++cy)
+      for (int cx = 0; cx < cw; ++cx) {
+        const float sx = (cx + 0.5f - f.ox) / f.scale - 0.5f, sy = (cy + 0.5f - f.oy) / f.scale - 0.5f;
+        if (sx < -0.5f || sy < -0.5f || sx > w - 0.5f || sy > h - 0.5f) continue;
+        const int x0 = std::max(0, std::min(w - 1, (int)std::floor(sx))), y0 = std::max(0, std::min(h - 1, (int)std::floor(sy)));
+        const int x1 = std::min(w - 1, x0 + 1), y1 = std::min(h - 1, y0 + 1);
+        const float ax = std::min(1.0f, std::max(0.0f, sx - x0)), ay = std::min(1.0f, std::max(0.0f, sy - y0));
+        const float v = (at(x0, y0) * (1 - ax) + at(x1, y0) * ax) * (1 - ay) + (at(x0, y1) * (1 - ax) + at(x1, y1) * ax) * ay;
+        const uint8_t g = (uint8_t)std::lround(std::min(255.0f, std::max(0.0f, (v - lo) * inv)));
+        uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
+        px[0] = px[1] = px[2] = g;
+      }
+  }
+ private:
+  std::shared_ptr<ImageRenderer> me() { return std::static_pointer_cast<ImageRenderer>(shared_from_this()); }
+};
+
+class SegmentationRenderer : public Renderer {
+ public:
+  // SegmentationRenderer::create(labelColors, 0.6f, 1.0f, 2)  main_sequential.cpp:261
+  static std::shared_ptr<SegmentationRenderer> create(LabelColors colors = {}, float opacity = 0.5f, float borderOpacity = 0.5f,
+                                                      int borderRadius = 1) {
+    return std::shared_ptr<SegmentationRenderer>(new SegmentationRenderer(std::move(colors), opacity, borderOpacity, borderRadius));
+  }
+  std::shared_ptr<SegmentationRenderer> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return me(); }
+  std::shared_ptr<SegmentationRenderer> addInputData(std::shared_ptr<Image> d) { connectData(std::move(d)); return me(); }
+  void paint(uint8_t* rgb, int cw, int ch) override {
+    auto img = inputImage();
+    if (img->getDataType() != TYPE_UINT8) throw Exception("SegmentationRenderer needs a uint8 label image");
+    const int w = img->getWidth(), h = img->getHeight();
+    const uint8_t* lab = img->as<uint8_t>();
+    const Fit f = fit(w, h, cw, ch);
+    auto label_at = [&](int x, int y) -> int { return (x < 0 || y < 0 || x >= w || y >= h) ? 0 : lab[(size_t)y * w + x]; };
+    for (int cy = 0; cy < ch; ++cy)
+      for (int cx = 0; cx < cw; ++cx) {
+        const int x = (int)std::floor((cx + 0.5f - f.ox) / f.scale), y = (int)std::floor((cy + 0.5f - f.oy) / f.scale);
+        const int l = label_at(x, y);
+        auto it = colors_.find(l);
+        if (l == 0 || it == colors_.end()) continue;
+        bool border = false;  // within borderRadius of a pixel with another label
+        for (int b = -radius_; b <= radius_ && !border; ++b)
+          for (int a = -radius_; a <= radius_ && !border; ++a)
+            if (a * a + b * b <= radius_ * radius_ && label_at(x + a, y + b) != l) border = true;
+        const float op = border ? borderOpacity_ : opacity_;
+        uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
+        const float c[3] = {it->second.r, it->second.g, it->second.b};
+        for (int k = 0; k < 3; ++k) px[k] = (uint8_t)std::lround(px[k] * (1 - op) + 255.0f * c[k] * op);
+      }
+  }
+ private:
+  SegmentationRenderer(LabelColors c, float o, float bo, int r) : colors_(std::move(c)), opacity_(o), borderOpacity_(bo), radius_(r) {}
+  std::shared_ptr<SegmentationRenderer> me() { return std::static_pointer_cast<SegmentationRenderer>(shared_from_this()); }
+  LabelColors colors_;
+  float opacity_, borderOpacity_;
+  int radius_;
+};
+
+class RenderToImage : public ProcessObject {
+ public:
+  static std::shared_ptr<RenderToImage> create(Color bg = Color::Black(), int width = 512, int height = 512) {
+    return std::shared_ptr<RenderToImage>(new RenderToImage(bg, width, height));
+  }
+  std::shared_ptr<RenderToImage> connect(std::shared_ptr<Renderer> r) { renderers_.push_back(std::move(r)); output_.reset(); return me(); }
+  void removeAllRenderers() { renderers_.clear(); output_.reset(); }
+  void update() override { evaluate(); }
+ protected:
+  void evaluate() override {
+    auto img = std::make_shared<Image>(w_, h_, TYPE_UINT8, 3);
+    uint8_t* rgb = img->as<uint8_t>();
+    for (size_t i = 0; i < (size_t)w_ * h_; ++i) {
+      rgb[3 * i] = (uint8_t)std::lround(bg_.r * 255); rgb[3 * i + 1] = (uint8_t)std::lround(bg_.g * 255); rgb[3 * i + 2] = (uint8_t)std::lround(bg_.b * 255);
+    }
+    for (auto& r : renderers_) r->paint(rgb, w_, h_);
+    output_ = img;
+  }
+ private:
+  RenderToImage(Color bg, int w, int h) : ProcessObject(RENDER_TO_IMAGE), bg_(bg), w_(w), h_(h) {}
+  std::shared_ptr<RenderToImage> me() { return std::static_pointer_cast<RenderToImage>(shared_from_this()); }
+  Color bg_;
+  int w_, h_;
+  std::vector<std::shared_ptr<Renderer>> renderers_;
+};
+
+class ImageFileExporter : public Typed<ImageFileExporter> {
+ public:
+  void update() override {
+    auto img = inputImage();
+    if (img->getDataType() != TYPE_UINT8) throw Exception("ImageFileExporter: only 8-bit images can be written as JPEG");
+    const int ch = img->getNrOfChannels();
+    try {
+      if (ch == 3) {  // the canvases rendered here are grey; store one component when all three agree
+        const uint8_t* p = img->as<uint8_t>();
+        const size_t n = (size_t)img->getWidth() * img->getHeight();
+        bool grey = true;
+        for (size_t i = 0; i < n && grey; ++i) grey = p[3 * i] == p[3 * i + 1] && p[3 * i] == p[3 * i + 2];
+        if (grey) {
+          std::vector<uint8_t> g(n);
+          for (size_t i = 0; i < n; ++i) g[i] = p[3 * i];
+          jpeg::save(file_, g.data(), img->getWidth(), img->getHeight(), 1);
+          return;
+        }
+      }
+      jpeg::save(file_, img->as<uint8_t>(), img->getWidth(), img->getHeight(), ch);
+    } catch (const std::exception& e) {
+      throw Exception(e.what());
+    }
+  }
+ protected:
+  friend class Typed<ImageFileExporter>;
+  explicit ImageFileExporter(std::string file) : Typed(EXPORTER), file_(std::move(file)) {}
+  std::string file_;
+};
+
+// The 5-pane GUI of test_pipeline.cpp:148-158 needs a window system; it is left out (no graphics
+// stack on this box).  run() returns immediately so the export stage that follows still executes.
+class MultiViewWindow {
+ public:
+  static std::shared_ptr<MultiViewWindow> create(int, Color = Color::Black(), int = 0, int = 0, bool = false) {
+    return std::make_shared<MultiViewWindow>();
+  }
+  void addRenderer(int, std::shared_ptr<Renderer>) {}
+  void setTitle(const std::string&) {}
+  void run() {}
+};
+
+}  // namespace nm03

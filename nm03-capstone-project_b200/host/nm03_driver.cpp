@@ -1,0 +1,344 @@
+// nm03_driver.cpp — B200-native batch driver with the shape of the reference's executables.
+//
+//   --mode parallel    img_processing_parallel   (src/parallel/main_parallel.cpp): patients sharded over
+//                      the GPUs by contiguous ranges, one feeder per GPU stream slot, whole-patient
+//                      batches through nm03_process_batch, JPEG export on host worker threads
+//   --mode sequential  img_processing_sequential (src/sequential/main_sequential.cpp): one slice at a time
+//   --test-pipeline F  test_pipeline            (src/test/test_pipeline.cpp): one slice, erosion branch,
+//                      five JPEGs (the GUI window is left out: no graphics stack)
+//   --make-dataset D   writes a synthetic cohort  D/PGBM-%03d/<series>/1-%02d.dcm  
+//
+// Kept from the reference: PGBM-* discovery (main_sequential.cpp:93-119), first series directory
+// (:138-139), numeric file ordering with fallback 1000 (:18-30,152-154), clean per-patient output
+// directory (:32-47), <stem>_original.jpg / <stem>_processed.jpg (:55-73), catch-and-continue with
+// per-patient success counts (:286-299).  Not kept: system("mkdir/rm") (std::filesystem instead).
+#include <nm03.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <filesystem>
+#include <future>
+#include <iostream>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "nm03.hpp"
+#include "phantom.hpp"
+
+namespace fs = std::filesystem;
+using Clock = std::chrono::steady_clock;
+
+namespace {
+
+struct Options {
+  std::string mode = "parallel", data, out = "../out-parallel", test_file, make_dataset;
+  std::vector<int> gpus;
+  int batch = 25, streams = 2, host_threads = 0;
+  bool do_export = true, dump_masks = false, lowcontrast = false;
+  int patients = 20, slices = 24, size = 512;
+};
+
+// main_sequential.cpp:18-30
+int extractFileNumber(const std::string& filename) {
+  const size_t dash = filename.find_last_of('-'), dot = filename.find(".dcm");
+  if (dash != std::string::npos && dot != std::string::npos && dot > dash) {
+    try { return std::stoi(filename.substr(dash + 1, dot - dash - 1)); } catch (...) { return 1000; }
+  }
+  return 1000;
+}
+
+std::vector<std::string> findAllPatientDirectories(const std::string& base) {
+  std::vector<std::string> dirs;
+  for (const auto& e : fs::directory_iterator(base))
+    if (e.is_directory() && e.path().filename().string().rfind("PGBM-", 0) == 0) dirs.push_back(e.path().filename().string());
+  std::sort(dirs.begin(), dirs.end());
+  return dirs;
+}
+
+std::vector<std::string> loadDICOMFilesForPatient(const std::string& base, const std::string& patient) {
+  std::vector<std::string> series;
+  for (const auto& e : fs::directory_iterator(fs::path(base) / patient))
+    if (e.is_directory()) series.push_back(e.path().string());
+  if (series.empty()) throw std::runtime_error("No series directories found for patient: " + patient);
+  std::sort(series.begin(), series.end());  // the reference takes whatever directory_iterator yields first
+  std::vector<std::pair<std::string, int>> files;
+  for (const auto& e : fs::directory_iterator(series[0]))
+    if (e.path().extension() == ".dcm") files.push_back({e.path().string(), extractFileNumber(e.path().filename().string())});
+  std::stable_sort(files.begin(), files.end(), [](const auto& a, const auto& b) { return a.second < b.second; });
+  std::vector<std::string> out;
+  for (auto& f : files) out.push_back(f.first);
+  return out;
+}
+
+void setupOutputDirectory(const fs::path& dir) {
+  fs::create_directories(dir);
+  for (const auto& e : fs::directory_iterator(dir)) fs::remove_all(e.path());
+}
+
+// simple parallel-for over host threads
+template <class F>
+void parallel_for(int n, int threads, F&& f) {
+  if (threads <= 1 || n <= 1) { for (int i = 0; i < n; ++i) f(i); return; }
+  std::atomic<int> next{0};
+  std::vector<std::thread> pool;
+  for (int t = 0; t < std::min(threads, n); ++t)
+    pool.emplace_back([&] { for (int i; (i = next.fetch_add(1)) < n;) f(i); });
+  for (auto& t : pool) t.join();
+}
+
+struct Pinned {
+  void* p = nullptr;
+  size_t bytes = 0;
+  void reserve(size_t n) {
+    if (n <= bytes) return;
+    if (p) nm03_host_free(p);
+    if (nm03_host_alloc(&p, n) != NM03_OK) throw std::runtime_error(nm03_last_error());
+    bytes = n;
+  }
+  ~Pinned() { if (p) nm03_host_free(p); }
+};
+
+void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const uint8_t* mask, int w, int h) {
+  using namespace nm03;
+  const std::string stem = fs::path(file).stem().string();
+  auto orig = std::make_shared<Image>(w, h, is_unsigned ? TYPE_UINT16 : TYPE_INT16);
+  std::memcpy(orig->data(), raw, (size_t)w * h * 2);
+  auto seg = std::make_shared<Image>(w, h, TYPE_UINT8);
+  std::memcpy(seg->data(), mask, (size_t)w * h);
+  LabelColors colors;
+  colors[1] = Color::White();
+  auto rti = RenderToImage::create(Color::Black(), 512, 512);  // main_sequential.cpp:258
+  rti->connect(ImageRenderer::create()->addInputData(orig));
+  rti->update();
+  ImageFileExporter::create((dir / (stem + "_original.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
+  rti->removeAllRenderers();
+  rti->connect(SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->addInputData(seg));
+  rti->update();
+  ImageFileExporter::create((dir / (stem + "_processed.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
+}
+
+struct Totals {
+  std::atomic<long> ok{0}, total{0}, patients_ok{0};
+  std::mutex log;
+};
+
+// one patient: parse on host threads into pinned memory, one GPU call per group of equal-size slices, export
+void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::string& patient, Pinned& in, Pinned& out, Totals& tot) {
+  const fs::path outdir = fs::path(opt.out) / patient;
+  if (opt.do_export || opt.dump_masks) setupOutputDirectory(outdir);
+  const std::vector<std::string> files = loadDICOMFilesForPatient(opt.data, patient);
+  const int n = (int)files.size();
+  tot.total += n;
+  std::vector<nm03::dicom::Slice> slices(n);
+  std::vector<int> state(n, 0);  // 0 = parsed, <0 = failed
+  parallel_for(n, opt.host_threads, [&](int i) {
+    try { slices[i] = nm03::dicom::load(files[i]); }
+    catch (const std::exception& e) {
+      state[i] = -1;
+      std::lock_guard<std::mutex> lk(tot.log);
+      std::cerr << "Error processing file " << files[i] << ":\nDetailed error: " << e.what() << std::endl;
+    }
+  });
+  nm03_params params;
+  nm03_default_params(&params);
+  int ok = 0;
+  std::vector<char> done(n, 0);
+  for (int first = 0; first < n; ++first) {
+    if (done[first] || state[first] < 0) continue;
+    // group: same size and signedness, in file order, at most `batch` slices (main_parallel.cpp:330-333)
+    std::vector<int> idx;
+    for (int j = first; j < n && (int)idx.size() < opt.batch; ++j)
+      if (!done[j] && state[j] == 0 && slices[j].cols == slices[first].cols && slices[j].rows == slices[first].rows &&
+          slices[j].pixel_representation == slices[first].pixel_representation) { idx.push_back(j); done[j] = 1; }
+    const int w = slices[first].cols, h = slices[first].rows, m = (int)idx.size();
+    const size_t npx = (size_t)w * h;
+    in.reserve(m * npx * 2);
+    out.reserve(m * npx);
+    for (int j = 0; j < m; ++j) std::memcpy((uint8_t*)in.p + j * npx * 2, slices[idx[j]].pixels.data(), npx * 2);
+    params.input_unsigned = slices[first].pixel_representation == 0;
+    nm03_outputs o = {};
+    o.dilated = (uint8_t*)out.p;
+    std::vector<int> status(m, 0);
+    const int rc = nm03_process_batch(ctx, gpu, in.p, m, w, h, &params, nullptr, 0, &o, status.data());
+    if (rc != NM03_OK) {
+      std::lock_guard<std::mutex> lk(tot.log);
+      for (int j = 0; j < m; ++j)
+        std::cerr << "Error processing file " << files[idx[j]] << ":\nDetailed error: " << nm03_last_error() << std::endl;
+      continue;  // a failed group is skipped, the patient goes on (main_parallel.cpp:163-167)
+    }
+    ok += m;
+    if (opt.dump_masks)
+      for (int j = 0; j < m; ++j) {
+        FILE* f = std::fopen((outdir / (fs::path(files[idx[j]]).stem().string() + ".mask")).string().c_str(), "wb");
+        if (f) { std::fwrite((uint8_t*)out.p + j * npx, 1, npx, f); std::fclose(f); }
+      }
+    if (opt.do_export)
+      parallel_for(m, opt.host_threads, [&](int j) {
+        try {
+          exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
+                      (uint8_t*)out.p + j * npx, w, h);
+        } catch (const std::exception& e) {
+          std::lock_guard<std::mutex> lk(tot.log);
+          std::cerr << "Error in export stage: " << e.what() << std::endl;
+        }
+      });
+  }
+  tot.ok += ok;
+  tot.patients_ok += 1;
+  std::lock_guard<std::mutex> lk(tot.log);
+  std::cout << "Patient " << patient << " completed. Successfully processed " << ok << "/" << n << " images." << std::endl;
+}
+
+int runBatch(const Options& opt) {
+  const std::vector<std::string> patients = findAllPatientDirectories(opt.data);
+  std::cout << "Found " << patients.size() << " patient directories." << std::endl;
+  if (patients.empty()) return 0;
+  fs::create_directories(opt.out);
+  nm03_ctx* ctx = nullptr;
+  if (nm03_init(opt.gpus.empty() ? nullptr : opt.gpus.data(), (int)opt.gpus.size(), &ctx) != NM03_OK) {
+    std::cerr << "Fatal error: " << nm03_last_error() << std::endl;
+    return 1;
+  }
+  const int G = nm03_gpu_count(ctx), P = (int)patients.size();
+  const bool sequential = opt.mode == "sequential";
+  Totals tot;
+  const auto t0 = Clock::now();
+  std::vector<std::thread> feeders;
+  for (int g = 0; g < (sequential ? 1 : G); ++g) {
+    // contiguous patient range of GPU g
+    const int lo = sequential ? 0 : (int)((long)g * P / G), hi = sequential ? P : (int)((long)(g + 1) * P / G);
+    const int S = sequential ? 1 : opt.streams;
+    auto next = std::make_shared<std::atomic<int>>(lo);
+    for (int s = 0; s < S; ++s)
+      feeders.emplace_back([&, g, hi, next] {
+        Pinned in, out;
+        for (int i; (i = next->fetch_add(1)) < hi;) {
+          try {
+            if (sequential) {
+              Options one = opt;
+              one.batch = 1;  // one slice per GPU call, as the reference's serial loop does
+              one.host_threads = 1;
+              processPatient(ctx, g, one, patients[i], in, out, tot);
+            } else {
+              processPatient(ctx, g, opt, patients[i], in, out, tot);
+            }
+          } catch (const std::exception& e) {
+            std::lock_guard<std::mutex> lk(tot.log);
+            std::cerr << "Error processing patient " << patients[i] << ": " << e.what() << std::endl;
+          }
+        }
+      });
+  }
+  for (auto& t : feeders) t.join();
+  const double sec = std::chrono::duration<double>(Clock::now() - t0).count();
+  std::cout << "\n=== All Processing Completed ===\n\nSuccessfully processed " << tot.patients_ok << "/" << P << " patients." << std::endl;
+  std::printf("{\"mode\": \"%s\", \"gpus\": %d, \"patients\": %d, \"slices\": %ld, \"ok\": %ld, \"seconds\": %.4f, "
+              "\"slices_per_sec\": %.1f, \"export\": %s}\n",
+              opt.mode.c_str(), sequential ? 1 : G, P, tot.total.load(), tot.ok.load(), sec, tot.ok.load() / sec,
+              opt.do_export ? "true" : "false");
+  nm03_shutdown(ctx);
+  return 0;
+}
+
+int runTestPipeline(const Options& opt) {
+  // the reference prototype through the FAST-shaped shim (test_pipeline.cpp:33-177), no window
+  using namespace nm03;
+  auto importer = DICOMFileImporter::create(opt.test_file);
+  importer->setLoadSeries(false);
+  importer->update();
+  auto image = importer->getOutputData<Image>(0);
+  const int width = image->getWidth(), height = image->getHeight();
+  auto normalize = IntensityNormalization::create(0.5f, 2.5f, 0.0f, 10000.0f)->connect(importer);
+  auto clipping = IntensityClipping::create(0.68f, 4000.0f)->connect(normalize);
+  auto median = VectorMedianFilter::create(7)->connect(clipping);
+  auto sharpen = ImageSharpening::create(2.0f, 0.5f, 9)->connect(median);
+  std::vector<int> seeds(2 * 512);
+  const int ns = nm03_make_seeds(width, height, seeds.data(), 512);
+  if (ns < 0) throw Exception(nm03_last_error());
+  std::vector<Vector3i> pts;
+  for (int i = 0; i < ns; ++i) pts.push_back(Vector3i(seeds[2 * i], seeds[2 * i + 1], 0));
+  auto rg = SeededRegionGrowing::create(0.74f, 0.91f, pts)->connect(sharpen);
+  auto caster = ImageCaster::create(TYPE_UINT8)->connect(rg);
+  auto erosion = Erosion::create(3)->connect(caster);
+  erosion->update();
+  auto dilation = Dilation::create(3)->connect(caster);
+  dilation->update();
+  LabelColors colors;
+  colors[1] = Color::White();
+  setupOutputDirectory(opt.out);
+  auto rti = RenderToImage::create(Color::Black(), 512, 512);
+  std::vector<std::pair<std::string, std::shared_ptr<Renderer>>> pairs = {
+      {"original_image", ImageRenderer::create()->connect(importer)},
+      {"preprocessed_image", ImageRenderer::create()->connect(sharpen)},
+      {"segmentation", SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->connect(rg)},
+      {"erosion_result", SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->connect(erosion)},
+      {"final_dilated_result", SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->connect(dilation)}};
+  for (auto& [name, r] : pairs) {
+    rti->removeAllRenderers();
+    rti->connect(r);
+    rti->update();
+    ImageFileExporter::create(opt.out + "/" + name + ".jpg")->connect(rti->getOutputData<Image>(0))->update();
+  }
+  std::cout << "test pipeline: " << width << "x" << height << ", 5 images written to " << opt.out << std::endl;
+  return 0;
+}
+
+int makeDataset(const Options& opt) {
+  for (int p = 0; p < opt.patients; ++p) {
+    char name[64];
+    std::snprintf(name, sizeof(name), "PGBM-%03d", p + 1);
+    const fs::path dir = fs::path(opt.make_dataset) / name / "01-01-2000-synthetic" ;
+    fs::create_directories(dir);
+    for (int s = 0; s < opt.slices; ++s) {
+      const std::vector<int16_t> px = nm03::phantom(opt.size, opt.size, p, s, opt.lowcontrast ? nm03::PHANTOM_LOWCONTRAST : nm03::PHANTOM_DEFAULT);
+      char fn[64];
+      std::snprintf(fn, sizeof(fn), "1-%02d.dcm", s + 1);
+      nm03::dicom::save((dir / fn).string(), (const uint16_t*)px.data(), opt.size, opt.size, true, s + 1, (p & 1) == 0);
+    }
+  }
+  std::cout << "wrote " << opt.patients << " patients x " << opt.slices << " slices " << opt.size << "x" << opt.size << " under "
+            << opt.make_dataset << std::endl;
+  return 0;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Options opt;
+  opt.data = nm03::Config::getTestDataPath() + "Brain-Tumor-Progression/T1-Post-Combined-P001-P020/";  // main_sequential.cpp:83-84
+  for (int i = 1; i < argc; ++i) {
+    const std::string a = argv[i];
+    auto val = [&]() -> std::string { if (i + 1 >= argc) { std::cerr << "missing value for " << a << std::endl; std::exit(2); } return argv[++i]; };
+    if (a == "--mode") opt.mode = val();
+    else if (a == "--data") opt.data = val();
+    else if (a == "--out") opt.out = val();
+    else if (a == "--gpus") { const std::string v = val(); for (size_t p = 0; p < v.size();) { opt.gpus.push_back(std::atoi(v.c_str() + p)); p = v.find(',', p); if (p == std::string::npos) break; ++p; } }
+    else if (a == "--batch") opt.batch = std::atoi(val().c_str());
+    else if (a == "--streams") opt.streams = std::atoi(val().c_str());
+    else if (a == "--host-threads") opt.host_threads = std::atoi(val().c_str());
+    else if (a == "--no-export") opt.do_export = false;
+    else if (a == "--dump-masks") opt.dump_masks = true;
+    else if (a == "--test-pipeline") opt.test_file = val();
+    else if (a == "--make-dataset") opt.make_dataset = val();
+    else if (a == "--patients") opt.patients = std::atoi(val().c_str());
+    else if (a == "--slices") opt.slices = std::atoi(val().c_str());
+    else if (a == "--size") opt.size = std::atoi(val().c_str());
+    else if (a == "--lowcontrast") opt.lowcontrast = true;
+    else { std::cerr << "unknown option " << a << std::endl; return 2; }
+  }
+  if (opt.host_threads <= 0) opt.host_threads = std::max(1u, std::thread::hardware_concurrency());
+  if (opt.mode == "sequential" && opt.out == "../out-parallel") opt.out = "../out-sequential";
+  try {
+    if (!opt.make_dataset.empty()) return makeDataset(opt);
+    if (!opt.test_file.empty()) { if (opt.out == "../out-parallel") opt.out = "../out-test"; return runTestPipeline(opt); }
+    return runBatch(opt);
+  } catch (const std::exception& e) {
+    std::cerr << "Fatal error: " << e.what() << std::endl;
+    return 1;
+  }
+}
