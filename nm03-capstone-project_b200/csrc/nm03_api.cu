@@ -37,6 +37,7 @@ int fail(int code, const char* fmt, ...) {
 
 constexpr int kSlots = 4;
 
+const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
@@ -175,6 +176,7 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   k.border_zero = p->border_mode == NM03_BORDER_ZERO;
   k.use_fma = p->sharpen_fma != 0;
   k.input_unsigned = p->input_unsigned != 0;
+  k.use_tma = g_no_tma ? 0 : 1;  // the launcher falls back to plain loads when the shape/alignment rules fail
   if (k.border_zero) {
     // outside-image samples are carried as the key -32768; real data is saturated to -32767, which is
     // only exact if f() does not distinguish the two lowest keys

@@ -39,6 +39,7 @@ struct PreParams {
   float clip_min, clip_max;
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
+  int use_tma;           // stage the raw halo tile with a TMA bulk tensor copy (needs w % 8 == 0, 16 B aligned input)
   float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
   // fast predicate path (no sharpened plane requested): separable blur with taps gx[-he..he] and a
   // proven bound eps = ea*|blur| + eb*|v| + ec on |sharpened_fast - sharpened_exact|; pixels closer

@@ -12,7 +12,10 @@
 // places where rounding must follow the oracle use explicit _rn intrinsics.
 #include "nm03_device.h"
 
+#include <cstring>
+
 #include <cooperative_groups.h>
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 namespace cg = cooperative_groups;
@@ -124,8 +127,35 @@ __device__ __noinline__ float blur1_exact(const float* __restrict__ Mc, const Pr
   return acc;
 }
 
+// ---- TMA helpers (cp.async.bulk.tensor + mbarrier, PTX ISA 8.x; SASS: UTMALDG / SYNCS) ------------
+__device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
 template <int K, int HS, int MODE>
-__global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p) {
+__global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p,
+                                                                         const __grid_constant__ CUtensorMap tmap) {
   constexpr int R = K / 2;
   constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
   constexpr int RW = K1_MW + 2 * R;        // raw columns actually needed
@@ -133,9 +163,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   static_assert(RW <= K1_PWS, "packed tile stride too small");
   static_assert(K1_MW % NM03_MEDIAN_RUN == 0, "median tile width must be a multiple of the run length");
 
-  extern __shared__ __align__(16) uint32_t smem[];
+  extern __shared__ __align__(16) uint32_t smem_raw[];
+  uint32_t* smem = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);  // TMA dst: 128 B
   uint32_t* P = smem;                                         // [PR][K1_PWS] packed keys (row q | row q+36 <<16)
-  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median)
+  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median); phase A: raw TMA tile
 
   const int tid = threadIdx.x;
   int tile = blockIdx.x;
@@ -149,8 +180,72 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   const uint32_t bias = p.input_unsigned ? 0x8000u : 0u;
 
   // ---- phase A: raw halo tile -> packed keys --------------------------------------------------
-  {
-    const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
+  const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
+  if (p.use_tma) {
+    // One bulk tensor copy brings the (MH+2R) x 144 int16 halo tile into shared memory (the float
+    // median tile's storage is free until phase B); rows/columns outside the image arrive as zeros.
+    // Without swizzle the innermost start coordinate must be a multiple of 16 bytes, so the box starts
+    // at x0-8 and raw column `col` of the tile sits at box column col + OFF.
+    constexpr int RH = K1_MH + 2 * R;
+    constexpr int OFF = 8 - K1_HS_MAX - R;
+    static_assert(OFF >= 0 && RW + OFF <= K1_PWS, "halo does not fit the aligned TMA box");
+    __shared__ __align__(8) uint64_t bar;
+    uint16_t* T = reinterpret_cast<uint16_t*>(M);   // [RH][K1_PWS] raw samples
+    if (tid == 0) mbar_init(&bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      mbar_expect_tx(&bar, RH * K1_PWS * 2);
+      tma_load_3d(T, &tmap, &bar, x0 - 8, gy0, slice);
+    }
+    mbar_wait(&bar, 0);
+    const bool interior = gx0 >= 0 && gy0 >= 0 && gx0 + RW <= w && gy0 + RH <= h;
+    if (!p.border_zero) {
+      // 4 packed words per thread: pixels i..i+3 of row q (low halves) and of row q+36 (high halves);
+      // the OFF-pixel shift is folded into the byte permutes
+      const uint32_t bias2 = bias | (bias << 16);
+      const uint32_t* Tw = reinterpret_cast<const uint32_t*>(T);
+      for (int idx = tid; idx < PR * (K1_PWS / 4); idx += K1_THREADS) {
+        const int q = idx / (K1_PWS / 4), c4 = idx - q * (K1_PWS / 4);
+        const int w0 = (4 * c4 + OFF) >> 1;                 // first 32-bit word holding pixel 4*c4 + OFF
+        const uint32_t* ra = Tw + q * (K1_PWS / 2) + w0;
+        const uint32_t* rb = Tw + (q + K1_MHP) * (K1_PWS / 2) + w0;
+        const bool last = w0 + 2 >= K1_PWS / 2;             // the word past the row end is never needed for real columns
+        const uint32_t a0 = ra[0], a1 = ra[1], a2 = last ? 0u : ra[2];
+        const uint32_t b0 = rb[0], b1 = rb[1], b2 = last ? 0u : rb[2];
+        uint4 o;
+        if ((OFF & 1) == 0) {
+          o.x = __byte_perm(a0, b0, 0x5410); o.y = __byte_perm(a0, b0, 0x7632);
+          o.z = __byte_perm(a1, b1, 0x5410); o.w = __byte_perm(a1, b1, 0x7632);
+        } else {
+          o.x = __byte_perm(a0, b0, 0x7632); o.y = __byte_perm(a1, b1, 0x5410);
+          o.z = __byte_perm(a1, b1, 0x7632); o.w = __byte_perm(a2, b2, 0x5410);
+        }
+        o.x ^= bias2; o.y ^= bias2; o.z ^= bias2; o.w ^= bias2;
+        *reinterpret_cast<uint4*>(P + q * K1_PWS + 4 * c4) = o;
+      }
+    }
+    if (!interior || p.border_zero) {
+      // border tile: patch the cells whose samples lie outside the image — replicate the image edge
+      // (clamp-to-edge) or insert the zero-border sentinel; zero mode also saturates real samples
+      if (!p.border_zero) __syncthreads();  // the vector pass above wrote other threads' cells
+      auto key = [&](int col, int row) -> uint32_t {
+        const int gx = gx0 + col, gy = gy0 + row;
+        if (p.border_zero) {
+          if (gx < 0 || gy < 0 || gx >= w || gy >= h) return 0x8000u;
+          const uint32_t v = (T[row * K1_PWS + min(col + OFF, K1_PWS - 1)] ^ bias) & 0xffffu;
+          return v == 0x8000u ? 0x8001u : v;
+        }
+        const int cx = clampi(clampi(gx, 0, w - 1) - gx0 + OFF, 0, K1_PWS - 1), cy = clampi(clampi(gy, 0, h - 1) - gy0, 0, RH - 1);
+        return (T[cy * K1_PWS + cx] ^ bias) & 0xffffu;
+      };
+      for (int idx = tid; idx < PR * K1_PWS; idx += K1_THREADS) {
+        const int q = idx / K1_PWS, col = idx - q * K1_PWS;
+        const int gx = gx0 + col, gya = gy0 + q, gyb = gya + K1_MHP;
+        if (!p.border_zero && gx >= 0 && gx < w && gya >= 0 && gyb < h) continue;  // both samples inside
+        P[idx] = key(col, q) | (key(col, q + K1_MHP) << 16);
+      }
+    }
+  } else {
     for (int idx = tid; idx < PR * K1_PWS; idx += K1_THREADS) {
       const int q = idx / K1_PWS, col = idx - q * K1_PWS;
       uint32_t a, b;
@@ -321,12 +416,44 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   }
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) f = nullptr;
+    return (EncodeTiledFn)f;
+  }();
+  return fn;
+}
+
+// tensor map over the [n][h][w] 16-bit batch with a (144, MH+2R, 1) box; false if TMA cannot be used
+static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
+  if ((p.w & 7) || ((uintptr_t)p.in & 15) || !encode_tiled_fn()) return false;
+  static_assert((size_t)K1_MH * K1_MW * 4 >= (size_t)(K1_MH + 6) * K1_PWS * 2, "raw tile must fit in the median tile storage");
+  const cuuint64_t dims[3] = {(cuuint64_t)p.w, (cuuint64_t)p.h, (cuuint64_t)p.n};
+  const cuuint64_t strides[2] = {(cuuint64_t)p.w * 2, (cuuint64_t)p.w * p.h * 2};
+  const cuuint32_t box[3] = {(cuuint32_t)K1_PWS, (cuuint32_t)(K1_MH + 2 * R), 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  return encode_tiled_fn()(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<void*>(p.in), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int K, int HS, int MODE>
-static cudaError_t launch_k1m(const PreParams& p, cudaStream_t s) {
+static cudaError_t launch_k1m(const PreParams& p0, cudaStream_t s) {
   constexpr int R = K / 2;
-  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4;
+  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + 128;
+  PreParams p = p0;
+  CUtensorMap map;
+  memset(&map, 0, sizeof(map));
+  p.use_tma = p0.use_tma && make_tmap(p, R, &map);
   const int grid = p.n * p.tiles_x * p.tiles_y;
-  k1_preprocess<K, HS, MODE><<<grid, K1_THREADS, smem, s>>>(p);
+  k1_preprocess<K, HS, MODE><<<grid, K1_THREADS, smem, s>>>(p, map);
   return cudaGetLastError();
 }
 
@@ -340,7 +467,7 @@ static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
-  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4);
+  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + 128);
   cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess && HS > 2)
