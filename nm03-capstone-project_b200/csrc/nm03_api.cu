@@ -54,6 +54,10 @@ struct Slot {
   size_t stage_in_bytes = 0;
   void* stage_out = nullptr;      // scratch: device copy of outputs before D2H
   size_t stage_out_bytes = 0;
+  float* lut = nullptr;           // scratch: f(key) table of K1 for the parameters in lut_key
+  size_t lut_bytes = 0;
+  float lut_key[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  bool lut_valid = false;
   bool busy = false;
 };
 
@@ -125,6 +129,7 @@ int ensure(Slot* s, void** buf, size_t* have, size_t need) {
   if (*buf) CK(cudaFree(*buf));
   *buf = nullptr;
   *have = 0;
+  if (buf == (void**)&s->lut) s->lut_valid = false;
   const size_t want = need + need / 4;
   cudaError_t e = cudaMalloc(buf, want);
   if (e != cudaSuccess) return fail(NM03_ERR_NOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
@@ -176,6 +181,7 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   k.border_zero = p->border_mode == NM03_BORDER_ZERO;
   k.use_fma = p->sharpen_fma != 0;
   k.input_unsigned = p->input_unsigned != 0;
+  k.lut = nullptr;
   k.use_tma = g_no_tma ? 0 : 1;  // the launcher falls back to plain loads when the shape/alignment rules fail
   if (k.border_zero) {
     // outside-image samples are carried as the key -32768; real data is saturated to -32767, which is
@@ -342,6 +348,23 @@ int get_worker(nm03_ctx* ctx, int gpu, Worker** wk) {
   return NM03_OK;
 }
 
+// make sure the slot's f(key) table matches these parameters (rebuilt by a tiny kernel when they change)
+int ensure_lut(Worker* wk, Slot* s, cudaStream_t st, nm03::PreParams& pre) {
+  int rc;
+  if ((rc = ensure(s, (void**)&s->lut, &s->lut_bytes, 65536 * sizeof(float)))) return rc;
+  const float key[8] = {pre.norm_min, pre.norm_range, pre.norm_scale, pre.norm_low, pre.clip_min, pre.clip_max,
+                        (float)pre.border_zero, (float)pre.input_unsigned};
+  if (!s->lut_valid || memcmp(key, s->lut_key, sizeof(key)) != 0) {
+    pre.lut = nullptr;
+    CK(nm03::launch_build_lut(pre, s->lut, st));
+    wk->launches += 1;
+    memcpy(s->lut_key, key, sizeof(key));
+    s->lut_valid = true;
+  }
+  pre.lut = s->lut;
+  return NM03_OK;
+}
+
 // queue K1 + K23 for n device-resident slices on `st`
 int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h,
                      const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out) {
@@ -359,6 +382,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   const size_t pred_bytes = (size_t)n * h * pre.wpr * 4;
   if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pred_bytes))) return rc;
   if (s->used && st != s->stream) CK(cudaStreamWaitEvent(st, s->done, 0));  // scratch reuse across streams
+  if ((rc = ensure_lut(wk, s, st, pre))) return rc;
   pre.in = d_slices;
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
@@ -570,6 +594,7 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.pred) cudaFree(s.pred);
       if (s.stage_in) cudaFree(s.stage_in);
       if (s.stage_out) cudaFree(s.stage_out);
+      if (s.lut) cudaFree(s.lut);
       if (s.done) cudaEventDestroy(s.done);
       if (s.stream) cudaStreamDestroy(s.stream);
     }

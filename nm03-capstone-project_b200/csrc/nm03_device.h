@@ -39,6 +39,7 @@ struct PreParams {
   float clip_min, clip_max;
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
+  const float* lut;      // optional [65536]: f(key) for every 16-bit key (bit-identical to the arithmetic), else null
   int use_tma;           // stage the raw halo tile with a TMA bulk tensor copy (needs w % 8 == 0, 16 B aligned input)
   float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
   // fast predicate path (no sharpened plane requested): separable blur with taps gx[-he..he] and a
@@ -82,6 +83,7 @@ cudaError_t launch_segment(const SegParams& p, cudaStream_t s);
 cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float lo, float hi, uint32_t* bits,
                                   cudaStream_t s);
 cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* bits, cudaStream_t s);
+cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s);  // fills lut[65536] with f(key)
 cudaError_t configure_kernels();  // opt in to large dynamic shared memory; once per device
 
 }  // namespace nm03

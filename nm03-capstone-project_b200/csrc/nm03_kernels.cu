@@ -56,6 +56,19 @@ __device__ __forceinline__ float key_to_float(int key, const PreParams& p) {
   return fminf(fmaxf(o, p.clip_min), p.clip_max);
 }
 
+// f() for all 65536 keys, computed once per parameter set with exactly the operations above; K1 then
+// replaces ~30 instructions per pixel (IEEE division with its special-case scaffolding) by one
+// cached load.  lut index = the key's 16 bits as an unsigned number.
+__global__ void k_build_lut(const __grid_constant__ PreParams p, float* __restrict__ lut) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 65536) lut[i] = key_to_float((int)(short)i, p);
+}
+
+cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s) {
+  k_build_lut<<<256, 256, 0, s>>>(p, lut);
+  return cudaGetLastError();
+}
+
 template <int K>
 struct MedianRun;
 template <>
@@ -238,11 +251,18 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         const int cx = clampi(clampi(gx, 0, w - 1) - gx0 + OFF, 0, K1_PWS - 1), cy = clampi(clampi(gy, 0, h - 1) - gy0, 0, RH - 1);
         return (T[cy * K1_PWS + cx] ^ bias) & 0xffffu;
       };
-      for (int idx = tid; idx < PR * K1_PWS; idx += K1_THREADS) {
-        const int q = idx / K1_PWS, col = idx - q * K1_PWS;
-        const int gx = gx0 + col, gya = gy0 + q, gyb = gya + K1_MHP;
-        if (!p.border_zero && gx >= 0 && gx < w && gya >= 0 && gyb < h) continue;  // both samples inside
-        P[idx] = key(col, q) | (key(col, q + K1_MHP) << 16);
+      // columns [0, cl) and [cr, PWS) of the tile are outside the image; a packed row q holds image
+      // rows gy0+q and gy0+q+36
+      const int cl = p.border_zero ? K1_PWS : max(0, -gx0), cr = p.border_zero ? K1_PWS : min(K1_PWS, w - gx0);
+      const int warp = tid >> 5, ln = tid & 31;
+      for (int q = warp; q < PR; q += K1_THREADS / 32) {
+        const int gya = gy0 + q, gyb = gya + K1_MHP;
+        if (gya < 0 || gyb >= h || gya >= h || gyb < 0 || p.border_zero) {
+          for (int col = ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+        } else {
+          for (int col = ln; col < cl; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          for (int col = cr + ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+        }
       }
     }
   } else {
@@ -272,10 +292,18 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       for (int c = 0; c < NM03_MEDIAN_RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
     MedianRun<K>::run(v, o);
     float lo[NM03_MEDIAN_RUN], hi[NM03_MEDIAN_RUN];
+    if (p.lut) {
 #pragma unroll
-    for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
-      lo[i] = key_to_float((int)(short)(o[i] & 0xffffu), p);
-      hi[i] = key_to_float((int)(short)(o[i] >> 16), p);
+      for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
+        lo[i] = __ldg(p.lut + (o[i] & 0xffffu));
+        hi[i] = __ldg(p.lut + (o[i] >> 16));
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
+        lo[i] = key_to_float((int)(short)(o[i] & 0xffffu), p);
+        hi[i] = key_to_float((int)(short)(o[i] >> 16), p);
+      }
     }
     float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
     float* mhi = mlo + K1_MHP * K1_MW;
@@ -292,17 +320,21 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // replicated raw samples).
   const int mx0 = x0 - K1_HS_MAX, my0 = y0 - K1_HS_MAX;
   if (mx0 < 0 || my0 < 0 || mx0 + K1_MW > w || my0 + K1_MH > h) {
-    for (int idx = tid; idx < K1_MH * K1_MW; idx += K1_THREADS) {
-      const int my = idx / K1_MW, mx = idx - my * K1_MW;
-      const int gx = mx0 + mx, gy = my0 + my;
-      if (gx < 0 || gy < 0 || gx >= w || gy >= h) {
-        float val = 0.0f;
-        if (!p.border_zero) {
-          const int cx = clampi(gx, 0, w - 1) - mx0, cy = clampi(gy, 0, h - 1) - my0;
-          // tiles that start beyond the image never reach here with a valid centre; guard anyway
-          val = (cx >= 0 && cy >= 0 && cx < K1_MW && cy < K1_MH) ? M[cy * K1_MW + cx] : 0.0f;
-        }
-        M[idx] = val;
+    // columns [0, cl) and [cr, MW) and rows [0, rt) and [rb, MH) of the tile lie outside the image
+    const int cl = max(0, -mx0), cr = min(K1_MW, w - mx0), rt = max(0, -my0), rb = min(K1_MH, h - my0);
+    const int warp = tid >> 5, ln = tid & 31;
+    auto fill = [&](int my, int mx, int cy) {
+      float val = 0.0f;
+      if (!p.border_zero && rb > rt && cr > cl) val = M[cy * K1_MW + clampi(mx, cl, cr - 1)];  // reads in-image cells only
+      M[my * K1_MW + mx] = val;                                                                 // writes outside cells only
+    };
+    for (int my = warp; my < K1_MH; my += K1_THREADS / 32) {
+      const int cy = clampi(my, rt, rb - 1);
+      if (my < rt || my >= rb) {
+        for (int mx = ln; mx < K1_MW; mx += 32) fill(my, mx, cy);
+      } else {
+        for (int mx = ln; mx < cl; mx += 32) fill(my, mx, cy);
+        for (int mx = cr + ln; mx < K1_MW; mx += 32) fill(my, mx, cy);
       }
     }
     __syncthreads();
