@@ -38,6 +38,7 @@ int fail(int code, const char* fmt, ...) {
 constexpr int kSlots = 4;
 
 const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
+const bool g_no_skip = [] { const char* e = getenv("NM03_NO_SKIP"); return e && e[0] == '1'; }();  // A/B measurements
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
@@ -182,7 +183,22 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   k.use_fma = p->sharpen_fma != 0;
   k.input_unsigned = p->input_unsigned != 0;
   k.lut = nullptr;
-  k.use_tma = g_no_tma ? 0 : 1;  // the launcher falls back to plain loads when the shape/alignment rules fail
+  k.use_tma = g_no_tma ? 0 : 1;
+  // clip floor shortcut: the largest key K with f(K) == f(lowest key); f must be non-decreasing in the
+  // key (both normalisation factors of one sign) and the zero-border sentinel must not be in play
+  k.skip_on = 0; k.skip_key2 = 0; k.skip_val = 0.0f;
+  if (!g_no_skip && !k.border_zero && (double)k.norm_scale * (double)k.norm_range > 0.0) {
+    const int kmin = -32768, off = k.input_unsigned ? 32768 : 0;
+    const float fmin_ = f_host((float)(kmin + off), p);
+    int lo = kmin, hi = 32767;                        // invariant: f(lo) == fmin_
+    if (f_host((float)(hi + off), p) == fmin_) lo = hi;
+    while (hi - lo > 1) { const int mid = lo + (hi - lo) / 2; if (f_host((float)(mid + off), p) == fmin_) lo = mid; else hi = mid; }
+    if (lo > kmin) {
+      k.skip_on = 1;
+      k.skip_key2 = ((uint32_t)lo & 0xffffu) | ((uint32_t)lo << 16);
+      k.skip_val = fmin_;
+    }
+  }  // the launcher falls back to plain loads when the shape/alignment rules fail
   if (k.border_zero) {
     // outside-image samples are carried as the key -32768; real data is saturated to -32767, which is
     // only exact if f() does not distinguish the two lowest keys

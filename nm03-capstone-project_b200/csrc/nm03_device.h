@@ -40,6 +40,11 @@ struct PreParams {
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
   const float* lut;      // optional [65536]: f(key) for every 16-bit key (bit-identical to the arithmetic), else null
+  // windows whose samples all have key <= skip_key map to f() == skip_val, so their median is known
+  // without sorting (clip floor; 0 = off).  skip_key2 = the key replicated in both 16-bit halves.
+  int skip_on;
+  uint32_t skip_key2;
+  float skip_val;
   int use_tma;           // stage the raw halo tile with a TMA bulk tensor copy (needs w % 8 == 0, 16 B aligned input)
   float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
   // fast predicate path (no sharpened plane requested): separable blur with taps gx[-he..he] and a

@@ -282,7 +282,58 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   __syncthreads();
 
   // ---- phase B: median of the K x K window on packed keys, then f() ---------------------------
-  for (int it = tid; it < K1_MHP * NRUN; it += K1_THREADS) {
+  // Work items (packed row, run of 8 columns).  An item whose whole input footprint lies at or below
+  // the clip floor has a known result (skip_val) and is not sorted: 8x8-block maxima of the packed
+  // tile decide that, and the remaining items are compacted into a list so that warps stay full.
+  __shared__ uint32_t blkmax[(PR + 7) / 8][K1_PWS / 8];
+  __shared__ uint16_t worklist[K1_MHP * NRUN];
+  __shared__ int n_work;
+  if (p.skip_on) {
+    if (tid == 0) n_work = 0;
+    for (int bidx = tid; bidx < ((PR + 7) / 8) * (K1_PWS / 8); bidx += K1_THREADS) {
+      const int g = bidx / (K1_PWS / 8), c8 = bidx - g * (K1_PWS / 8);
+      uint32_t m = 0x80008000u;  // (-32768, -32768)
+      for (int q = 8 * g; q < min(PR, 8 * g + 8); ++q) {
+        const uint4 a = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8);
+        const uint4 c = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8 + 4);
+        m = __vimax3_s16x2(m, __vmaxs2(a.x, a.y), __vmaxs2(a.z, a.w));
+        m = __vimax3_s16x2(m, __vmaxs2(c.x, c.y), __vmaxs2(c.z, c.w));
+      }
+      blkmax[g][c8] = m;
+    }
+    __syncthreads();
+    const int lane = tid & 31;
+    for (int base = 0; base < K1_MHP * NRUN; base += K1_THREADS) {   // trip count is block-uniform
+      const int it = base + tid;
+      bool need = false;
+      if (it < K1_MHP * NRUN) {
+        const int prow = it / NRUN, run = it - prow * NRUN;
+        // footprint: packed rows prow .. prow+K-1, columns run*RUN .. run*RUN + RUN+K-2
+        const int g0 = prow >> 3, g1 = (prow + K - 1) >> 3;
+        const int c0 = (run * NM03_MEDIAN_RUN) >> 3, c1 = (run * NM03_MEDIAN_RUN + NM03_MEDIAN_RUN + K - 2) >> 3;
+        uint32_t m = __vmaxs2(__vmaxs2(blkmax[g0][c0], blkmax[g0][c1]), __vmaxs2(blkmax[g1][c0], blkmax[g1][c1]));
+        need = __vmaxs2(m, p.skip_key2) != p.skip_key2;        // some sample above the floor, in either half
+        if (!need) {
+          float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
+          const float4 f4 = make_float4(p.skip_val, p.skip_val, p.skip_val, p.skip_val);
+#pragma unroll
+          for (int i = 0; i < NM03_MEDIAN_RUN; i += 4) {
+            *reinterpret_cast<float4*>(mlo + i) = f4;
+            *reinterpret_cast<float4*>(mlo + K1_MHP * K1_MW + i) = f4;
+          }
+        }
+      }
+      const uint32_t bal = __ballot_sync(0xffffffffu, need);
+      int slot = 0;
+      if (lane == 0 && bal) slot = atomicAdd(&n_work, __popc(bal));
+      slot = __shfl_sync(0xffffffffu, slot, 0);
+      if (need) worklist[slot + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)it;
+    }
+    __syncthreads();
+  }
+  const int n_items = p.skip_on ? n_work : K1_MHP * NRUN;
+  for (int wi = tid; wi < n_items; wi += K1_THREADS) {
+    const int it = p.skip_on ? worklist[wi] : wi;
     const int prow = it / NRUN, run = it - prow * NRUN;
     uint32_t v[NM03_MEDIAN_RUN + K - 1][K], o[NM03_MEDIAN_RUN];
     const uint32_t* src = P + prow * K1_PWS + run * NM03_MEDIAN_RUN;
