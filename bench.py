@@ -328,6 +328,18 @@ def main():
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
         # K1 in this configuration must read 2 B/px of int16 and write the 1-bit/px predicate plane
         k1_bytes = SLICES * W * H * (2.0 + 1.0 / 8.0)
+        # DRAM traffic of one K1 launch from the latest committed `ncu --set full` capture of this command
+        traffic, traffic_src = None, None
+        try:
+            import glob
+            cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_summary.json")))
+            if cand:
+                summ = json.load(open(cand[-1]))
+                k1s = next(v for k, v in summ.items() if k.startswith("k1_preprocess"))
+                traffic = k1s["dram_read_bytes"] + k1s["dram_write_bytes"]
+                traffic_src = "profiles/" + os.path.basename(cand[-1])
+        except Exception:
+            pass
         k1_avg_ms = k1_ms / max(calls, 1)
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
         oracle = load_oracle()
@@ -346,7 +358,8 @@ def main():
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "k1_preprocess<7,4>", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "avg_launch_ms": k1_avg_ms, "bytes_per_launch": k1_bytes,
                          "share_of_step": k1_ms / ms if ms > 0 else None,
                          "k23_avg_launch_ms": k23_ms / max(calls, 1),
