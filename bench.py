@@ -36,6 +36,15 @@ UNIT = "slices/s"
 WORKLOAD = "one synthetic patient series: 24 slices 512x512 int16, default median/sharpen/dilation params"
 
 
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1 to its workers, which
+    is not what the reference's `omp_set_num_threads(16)` CPU run should be limited to)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def load_oracle():
     """CPU oracle — used ONLY for the cpu_baseline / --impl reference legs."""
     so = os.path.join(ROOT, "oracle", "libnm03_oracle.so")
@@ -186,7 +195,7 @@ def run_reference(args, rank):
     if rank != 0:
         return
     oracle = load_oracle()
-    threads = oracle.nm03o_max_threads()
+    threads = host_threads()
     series = numpy_series(1)
     for _ in range(args.warmup):
         time_cpu(oracle, series[:SLICES], threads, 0, 1)
@@ -335,7 +344,7 @@ def main():
             cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_summary.json")))
             if cand:
                 summ = json.load(open(cand[-1]))
-                k1s = next(v for k, v in summ.items() if k.startswith("k1_preprocess"))
+                k1s = next(v for k, v in summ.items() if "k1_preprocess" in k)
                 traffic = k1s["dram_read_bytes"] + k1s["dram_write_bytes"]
                 traffic_src = "profiles/" + os.path.basename(cand[-1])
         except Exception:
@@ -343,7 +352,7 @@ def main():
         k1_avg_ms = k1_ms / max(calls, 1)
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
         oracle = load_oracle()
-        threads = oracle.nm03o_max_threads()
+        threads = host_threads()
         cpu_val, reps, cpu_dt = time_cpu(oracle, h_in[0].copy(), threads, args.cpu_seconds, 1000)
         line = {
             "metric": METRIC, "value": world * args.steps * SLICES / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
