@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <mutex>
 #include <vector>
 
@@ -38,6 +39,7 @@ int fail(int code, const char* fmt, ...) {
 constexpr int kSlots = 4;
 
 const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
+const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); return e && e[0] == '1'; }();
 const bool g_no_skip = [] { const char* e = getenv("NM03_NO_SKIP"); return e && e[0] == '1'; }();  // A/B measurements
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
@@ -182,6 +184,21 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   k.border_zero = p->border_mode == NM03_BORDER_ZERO;
   k.use_fma = p->sharpen_fma != 0;
   k.input_unsigned = p->input_unsigned != 0;
+  // central tiles first (heaviest on brain slices), see PreParams::tile_order
+  k.tile_order_on = 0;
+  {
+    const int nt = k.tiles_x * k.tiles_y;
+    if (nt <= 256 && nt > 1 && !g_no_tile_order) {
+      std::vector<std::pair<double, int>> ord;
+      for (int t = 0; t < nt; ++t) {
+        const double cx = ((t % k.tiles_x) + 0.5) * nm03::K1_TW - 0.5 * w, cy = ((t / k.tiles_x) + 0.5) * nm03::K1_TH - 0.5 * h;
+        ord.push_back({(cx / w) * (cx / w) + (cy / h) * (cy / h), t});
+      }
+      std::stable_sort(ord.begin(), ord.end());
+      for (int t = 0; t < nt; ++t) k.tile_order[t] = (uint16_t)ord[t].second;
+      k.tile_order_on = 1;
+    }
+  }
   k.lut = nullptr;
   k.use_tma = g_no_tma ? 0 : 1;
   // clip floor shortcut: the largest key K with f(K) == f(lowest key); f must be non-decreasing in the

@@ -46,6 +46,10 @@ struct PreParams {
   uint32_t skip_key2;
   float skip_val;
   int use_tma;           // stage the raw halo tile with a TMA bulk tensor copy (needs w % 8 == 0, 16 B aligned input)
+  // launch order: block b works on tile tile_order[b / n] of slice b % n, central (busiest) tiles first,
+  // so the last, partially filled wave holds the cheap corner tiles (tile_order_on = 0: identity)
+  int tile_order_on;
+  uint16_t tile_order[256];
   float mask[81];        // normalised Gaussian, index x+hs + (y+hs)*m, m = 2*hs+1
   // fast predicate path (no sharpened plane requested): separable blur with taps gx[-he..he] and a
   // proven bound eps = ea*|blur| + eb*|v| + ec on |sharpened_fast - sharpened_exact|; pixels closer

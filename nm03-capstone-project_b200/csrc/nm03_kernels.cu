@@ -182,15 +182,18 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median); phase A: raw TMA tile
 
   const int tid = threadIdx.x;
-  int tile = blockIdx.x;
-  const int tx = tile % p.tiles_x;
-  tile /= p.tiles_x;
-  const int ty = tile % p.tiles_y;
-  const int slice = tile / p.tiles_y;
+  int slice, tile;
+  if (p.tile_order_on) { slice = blockIdx.x % p.n; tile = p.tile_order[blockIdx.x / p.n]; }
+  else { tile = blockIdx.x % (p.tiles_x * p.tiles_y); slice = blockIdx.x / (p.tiles_x * p.tiles_y); }
+  const int tx = tile % p.tiles_x, ty = tile / p.tiles_x;
   const int x0 = tx * K1_TW, y0 = ty * K1_TH;
   const int w = p.w, h = p.h;
   const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
   const uint32_t bias = p.input_unsigned ? 0x8000u : 0u;
+
+  // let a dependent kernel (K23, launched with programmatic serialization) be scheduled while this
+  // grid drains; it still waits in cudaGridDependencySynchronize() until this grid has completed
+  cudaTriggerProgrammaticLaunchCompletion();
 
   // ---- phase A: raw halo tile -> packed keys --------------------------------------------------
   const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
@@ -697,9 +700,12 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
 
   for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  // Launched with programmatic stream serialization: everything above overlaps the tail of the kernel
+  // that produces the predicate plane; its memory is only touched after this point.
+  cudaGridDependencySynchronize();
   for (int i = tid; i < rows * wpr; i += SEG_THREADS) {
     const int r = i / wpr, k = i - r * wpr;
-    uint32_t v = r < nrows ? __ldg(gp + (size_t)(y_begin + r) * wpr + k) : 0u;
+    uint32_t v = r < nrows ? __ldcg(gp + (size_t)(y_begin + r) * wpr + k) : 0u;
     if (k == wpr - 1) v &= lastmask;
     Pp[i] = v;
   }
@@ -841,13 +847,15 @@ cudaError_t launch_segment(const SegParams& p, cudaStream_t s) {
   cfg.blockDim = dim3(SEG_THREADS);
   cfg.dynamicSmemBytes = seg_smem_bytes(p.rows_per, p.wpr);
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = p.cluster;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   return cudaLaunchKernelEx(&cfg, k23_segment, p);
 }
 
