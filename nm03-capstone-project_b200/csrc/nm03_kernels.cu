@@ -609,9 +609,13 @@ __device__ __forceinline__ void store_word_u8(uint8_t* __restrict__ row, int x, 
 // read from shared memory as they are (chaotic relaxation of a monotone operator: any interleaving
 // converges to the same fixed point, and a pass without any change proves it has been reached).
 // MASKED = image-border pixels may be labelled but never act as sources (rg_border_expand = 0).
+// Activity flags: an item (row segment x word column) is processed in a pass only if it, or one of
+// the items it reads from, changed since it was last looked at; a changing item wakes itself and its
+// neighbours for the next pass.  Work is therefore proportional to the grown region, not to the image.
 template <bool CONN8, bool MASKED>
 __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32_t* __restrict__ Pp,
-                                         const SegParams& p, int nrows, int y_begin, int tid) {
+                                         const SegParams& p, int nrows, int y_begin, int tid,
+                                         uint8_t* __restrict__ act_now, uint8_t* __restrict__ act_next) {
   const int wpr = p.wpr;
 #define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
   const int lastk = (p.w - 1) >> 5;
@@ -619,6 +623,9 @@ __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32
   int changed = 0;
   const int nseg = (nrows + p.seg_rows - 1) / p.seg_rows;
   for (int it = tid; it < nseg * wpr; it += SEG_THREADS) {
+    if (!act_now[it]) continue;
+    act_now[it] = 0;
+    int item_changed = 0;
     const int sgi = it / wpr, k = it - sgi * wpr;
     const int ra = sgi * p.seg_rows, rb = min(nrows, ra + p.seg_rows);
     const bool has_l = k > 0, has_r = k < wpr - 1;
@@ -668,13 +675,25 @@ __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32
         } else {
           nw = hfill(cand, pw);
         }
-        if (nw != m) { MROW(r)[k] = nw; changed = 1; }
+        if (nw != m) { MROW(r)[k] = nw; item_changed = 1; }
         behind = here;
         behind.c = nw;
         behind.s = (MASKED && !src_here) ? 0u : nw & colmask;
         here = ahead;
         ahead = next;
         pw = pw_next;
+      }
+    }
+    if (item_changed) {
+      changed = 1;
+      act_next[it] = 1;
+      if (has_l) act_next[it - 1] = 1;
+      if (has_r) act_next[it + 1] = 1;
+      if (sgi > 0) act_next[it - wpr] = 1;
+      if (sgi < nseg - 1) act_next[it + wpr] = 1;
+      if (CONN8) {
+        if (sgi > 0) { if (has_l) act_next[it - wpr - 1] = 1; if (has_r) act_next[it - wpr + 1] = 1; }
+        if (sgi < nseg - 1) { if (has_l) act_next[it + wpr - 1] = 1; if (has_r) act_next[it + wpr + 1] = 1; }
       }
     }
   }
@@ -692,6 +711,9 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   // planes: predicate rows owned by this CTA; mask rows with SEG_HALO halo rows above and below
   uint32_t* Pp = smem;                                   // [rows][wpr]
   uint32_t* Mm = smem + (size_t)rows * wpr;              // [rows + 2*HALO][wpr]
+  const int nseg_max = (rows + p.seg_rows - 1) / p.seg_rows;
+  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * wpr);  // [nseg][wpr] x 2
+  uint8_t* act1 = act0 + (size_t)nseg_max * wpr;
   __shared__ int s_flag[3];                              // rotating "somebody changed" flags (see below)
 #define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
   const int y_begin = rank * rows;                       // first image row owned
@@ -700,6 +722,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
 
   for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  for (int i = tid; i < 2 * nseg_max * wpr; i += SEG_THREADS) act0[i] = 0;
   // Launched with programmatic stream serialization: everything above overlaps the tail of the kernel
   // that produces the predicate plane; its memory is only touched after this point.
   cudaGridDependencySynchronize();
@@ -719,7 +742,10 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
       const int sx = p.seeds[i].x, sy = p.seeds[i].y;
       if (!p.host_mode) {
         const int r = sy - y_begin;
-        if (r >= 0 && r < nrows) atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
+        if (r >= 0 && r < nrows) {
+          atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
+          act0[(r / p.seg_rows) * wpr + (sx >> 5)] = 1;
+        }
       } else {
         // FAST executeOnHost: the seed's neighbours are tested, not the seed itself
         const int ddx[8] = {0, 1, -1, 0, 1, -1, 1, -1}, ddy[8] = {1, 0, 0, -1, 1, 1, -1, -1};
@@ -728,6 +754,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
           const int r = ny - y_begin;
           if (nx < 0 || nx >= p.w || r < 0 || r >= nrows) continue;
           atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * wpr + (nx >> 5)]);
+          act0[(r / p.seg_rows) * wpr + (nx >> 5)] = 1;
         }
       }
     }
@@ -744,8 +771,10 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
     for (int q = 0;; ++q) {
       ++passes;
       int changed;
-      if (p.conn8) changed = masked ? fill_pass<true, true>(Mm, Pp, p, nrows, y_begin, tid) : fill_pass<true, false>(Mm, Pp, p, nrows, y_begin, tid);
-      else changed = masked ? fill_pass<false, true>(Mm, Pp, p, nrows, y_begin, tid) : fill_pass<false, false>(Mm, Pp, p, nrows, y_begin, tid);
+      uint8_t* an = (q & 1) ? act1 : act0;
+      uint8_t* ax = (q & 1) ? act0 : act1;
+      if (p.conn8) changed = masked ? fill_pass<true, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<true, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
+      else changed = masked ? fill_pass<false, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<false, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
       changed = __syncthreads_or(changed | hchg);
       if (C == 1) {
         if (!changed) break;
@@ -765,7 +794,18 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
         const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
         const uint32_t v = remote[(size_t)((side == 0 ? rows - 1 : 0) + SEG_HALO) * wpr + kk];
         uint32_t* mine = MROW(side == 0 ? -1 : rows) + kk;
-        if (*mine != v) { *mine = v; hchg = 1; }
+        if (*mine != v) {
+          *mine = v;
+          hchg = 1;
+          // the boundary segment next to that halo row has new input: wake it (and its word neighbours)
+          const int nsg = (nrows + p.seg_rows - 1) / p.seg_rows;
+          if (nsg > 0) {
+            uint8_t* row = ax + (side == 0 ? 0 : nsg - 1) * wpr;
+            row[kk] = 1;
+            if (kk > 0) row[kk - 1] = 1;
+            if (kk < wpr - 1) row[kk + 1] = 1;
+          }
+        }
       }
       __syncthreads();
     }
@@ -804,7 +844,12 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
     if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
     if (p.dilated) {
       uint32_t acc = m;
-      if (p.dil_n > 0) {
+      if (p.dil_n == 1 && p.dil_hw[0] == 0 && p.dil_hw[1] == 1) {   // Dilation(3) with the disc SE: the 5-pixel plus
+        const uint32_t* row = MROW(r);
+        acc = m | __funnelshift_r(m, has_r ? row[k + 1] : 0u, 1) | __funnelshift_l(has_l ? row[k - 1] : 0u, m, 1);
+        if (y > 0) acc |= MROW(r - 1)[k];
+        if (y < p.h - 1) acc |= MROW(r + 1)[k];
+      } else if (p.dil_n > 0) {
         acc = 0u;
         for (int b = -p.dil_n; b <= p.dil_n; ++b) {
           const int yy = y + b;
@@ -838,7 +883,8 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
 }
 
 size_t seg_smem_bytes(int rows_per, int wpr) {
-  return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * wpr * 4;
+  // predicate + mask planes, plus two activity-flag arrays (at most one byte per row and word column)
+  return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * wpr * 4 + 2 * (size_t)rows_per * wpr;
 }
 
 cudaError_t launch_segment(const SegParams& p, cudaStream_t s) {
