@@ -88,28 +88,35 @@ struct BitWriter {
   void flush() { if (nbits > 0) put(0x7F, 8 - nbits); }
 };
 
-inline void fdct8x8(float* d) {
-  // separable 8-point DCT-II (direct form; 64 blocks of 4096 px are not a bottleneck next to entropy coding)
-  static float cs[8][8];
-  static bool init = false;
-  if (!init) {
-    for (int u = 0; u < 8; ++u)
-      for (int x = 0; x < 8; ++x) cs[u][x] = (u == 0 ? std::sqrt(0.125f) : 0.5f) * std::cos((2 * x + 1) * u * 3.14159265358979f / 16.0f);
-    init = true;
-  }
-  float t[64];
-  for (int y = 0; y < 8; ++y)
-    for (int u = 0; u < 8; ++u) {
-      float s = 0;
-      for (int x = 0; x < 8; ++x) s += cs[u][x] * d[y * 8 + x];
-      t[y * 8 + u] = s;
-    }
-  for (int u = 0; u < 8; ++u)
-    for (int v = 0; v < 8; ++v) {
-      float s = 0;
-      for (int y = 0; y < 8; ++y) s += cs[v][y] * t[y * 8 + u];
-      d[v * 8 + u] = s;
-    }
+// 8-point forward DCT after Arai, Agui and Nakajima: 5 multiplications and 29 additions per
+// transform; the outputs are scaled by kAan[u] (times 8 for the 2-D transform), which the caller folds
+// into its reciprocal quantisation table.
+static const float kAan[8] = {1.0f, 1.387039845f, 1.306562965f, 1.175875602f, 1.0f, 0.785694958f, 0.541196100f, 0.275899379f};
+
+inline void aan8(float* d, int stride) {
+  const float t0 = d[0] + d[7 * stride], t7 = d[0] - d[7 * stride];
+  const float t1 = d[stride] + d[6 * stride], t6 = d[stride] - d[6 * stride];
+  const float t2 = d[2 * stride] + d[5 * stride], t5 = d[2 * stride] - d[5 * stride];
+  const float t3 = d[3 * stride] + d[4 * stride], t4 = d[3 * stride] - d[4 * stride];
+  const float e0 = t0 + t3, e3 = t0 - t3, e1 = t1 + t2, e2 = t1 - t2;
+  d[0] = e0 + e1;
+  d[4 * stride] = e0 - e1;
+  const float z1 = (e2 + e3) * 0.707106781f;
+  d[2 * stride] = e3 + z1;
+  d[6 * stride] = e3 - z1;
+  const float o0 = t4 + t5, o1 = t5 + t6, o2 = t6 + t7;
+  const float z5 = (o0 - o2) * 0.382683433f;
+  const float z2 = 0.541196100f * o0 + z5, z4 = 1.306562965f * o2 + z5, z3 = o1 * 0.707106781f;
+  const float z11 = t7 + z3, z13 = t7 - z3;
+  d[5 * stride] = z13 + z2;
+  d[3 * stride] = z13 - z2;
+  d[stride] = z11 + z4;
+  d[7 * stride] = z11 - z4;
+}
+
+inline void fdct8x8_scaled(float* d) {
+  for (int y = 0; y < 8; ++y) aan8(d + 8 * y, 1);
+  for (int x = 0; x < 8; ++x) aan8(d + x, 8);
 }
 
 inline void marker(std::vector<uint8_t>& o, uint8_t m, const std::vector<uint8_t>& payload) {
@@ -132,6 +139,12 @@ inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height,
     int a = (kQLuma[i] * scale + 50) / 100, b = (kQChroma[i] * scale + 50) / 100;
     q[0][i] = (uint8_t)(a < 1 ? 1 : (a > 255 ? 255 : a));
     q[1][i] = (uint8_t)(b < 1 ? 1 : (b > 255 ? 255 : b));
+  }
+  float rq[2][64];  // reciprocal quantiser including the DCT's output scaling
+  for (int i = 0; i < 64; ++i) {
+    const float sc = 1.0f / (kAan[i >> 3] * kAan[i & 7] * 8.0f);
+    rq[0][i] = sc / q[0][i];
+    rq[1][i] = sc / q[1][i];
   }
   static Huff hdc[2], hac[2];
   static bool built = false;
@@ -177,6 +190,12 @@ inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height,
   for (int by = 0; by < height; by += 8)
     for (int bx = 0; bx < width; bx += 8)
       for (int c = 0; c < channels; ++c) {
+        if (channels == 1 && by + 8 <= height && bx + 8 <= width) {
+          for (int y = 0; y < 8; ++y) {
+            const uint8_t* px = pixels + (size_t)(by + y) * width + bx;
+            for (int x = 0; x < 8; ++x) blk[y * 8 + x] = (float)px[x] - 128.0f;
+          }
+        } else
         for (int y = 0; y < 8; ++y)
           for (int x = 0; x < 8; ++x) {
             const int sy = by + y < height ? by + y : height - 1, sx = bx + x < width ? bx + x : width - 1;
@@ -191,10 +210,21 @@ inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height,
             }
             blk[y * 8 + x] = v - 128.0f;
           }
-        fdct8x8(blk);
         const int t = c ? 1 : 0;
         int zz[64];
-        for (int i = 0; i < 64; ++i) zz[i] = (int)std::lround(blk[kZigzag[i]] / q[t][kZigzag[i]]);
+        bool flat = true;  // constant block (most of a rendered mask): only the DC term survives
+        for (int i = 1; i < 64 && flat; ++i) flat = blk[i] == blk[0];
+        if (flat) {
+          const float qv = blk[0] * 64.0f * rq[t][0];   // the scaled transform's DC output is the plain sum
+          zz[0] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+          for (int i = 1; i < 64; ++i) zz[i] = 0;
+        } else {
+          fdct8x8_scaled(blk);
+          for (int i = 0; i < 64; ++i) {
+            const float qv = blk[kZigzag[i]] * rq[t][kZigzag[i]];
+            zz[i] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+          }
+        }
         auto emit = [&](const Huff& h, int run_size, int value, int size) {
           bw.put(h.code[run_size], h.len[run_size]);
           if (size) bw.put((uint32_t)(value < 0 ? value - 1 : value), size);

@@ -455,31 +455,41 @@ class ImageRenderer : public Renderer {
   void paint(uint8_t* rgb, int cw, int ch) override {
     auto img = inputImage();
     const int w = img->getWidth(), h = img->getHeight();
-    auto at = [&](int x, int y) -> float {
-      const size_t i = (size_t)y * w + x;
-      switch (img->getDataType()) {
-        case TYPE_FLOAT: return img->as<float>()[i];
-        case TYPE_UINT8: return img->as<uint8_t>()[i];
-        case TYPE_UINT16: return img->as<uint16_t>()[i];
-        default: return img->as<int16_t>()[i];
-      }
-    };
-    float lo = at(0, 0), hi = lo;  // window = full intensity range of the image, level = its centre
-    for (int y = 0; y < h; ++y) for (int x = 0; x < w; ++x) { const float v = at(x, y); lo = std::min(lo, v); hi = std::max(hi, v); }
+    const size_t n = (size_t)w * h;
+    std::vector<float> v(n);  // one conversion pass, then plain float indexing
+    switch (img->getDataType()) {
+      case TYPE_FLOAT: std::memcpy(v.data(), img->as<float>(), n * 4); break;
+      case TYPE_UINT8: { const uint8_t* s = img->as<uint8_t>(); for (size_t i = 0; i < n; ++i) v[i] = s[i]; break; }
+      case TYPE_UINT16: { const uint16_t* s = img->as<uint16_t>(); for (size_t i = 0; i < n; ++i) v[i] = s[i]; break; }
+      default: { const int16_t* s = img->as<int16_t>(); for (size_t i = 0; i < n; ++i) v[i] = s[i]; break; }
+    }
+    float lo = v[0], hi = v[0];  // window = full intensity range of the image, level = its centre
+    for (size_t i = 0; i < n; ++i) { lo = std::min(lo, v[i]); hi = std::max(hi, v[i]); }
     const float inv = hi > lo ? 255.0f / (hi - lo) : 0.0f;
+    auto grey = [&](float x) { const float g = (x - lo) * inv; return (uint8_t)(int)(std::min(255.0f, std::max(0.0f, g)) + 0.5f); };
+    if (w == cw && h == ch) {  // canvas and image have the same size: the fit is the identity
+      for (size_t i = 0; i < n; ++i) { const uint8_t g = grey(v[i]); rgb[3 * i] = rgb[3 * i + 1] = rgb[3 * i + 2] = g; }
+      return;
+    }
     const Fit f = fit(w, h, cw, ch);
-    for (int cy = 0; cy < ch; ++cy)
+    const float is = 1.0f / f.scale;
+    for (int cy = 0; cy < ch; ++cy) {
+      const float sy = (cy + 0.5f - f.oy) * is - 0.5f;
+      if (sy < -0.5f || sy > h - 0.5f) continue;
+      const int y0 = std::max(0, std::min(h - 1, (int)std::floor(sy))), y1 = std::min(h - 1, y0 + 1);
+      const float ay = std::min(1.0f, std::max(0.0f, sy - y0));
       for (int cx = 0; cx < cw; ++cx) {
-        const float sx = (cx + 0.5f - f.ox) / f.scale - 0.5f, sy = (cy + 0.5f - f.oy) / f.scale - 0.5f;
-        if (sx < -0.5f || sy < -0.5f || sx > w - 0.5f || sy > h - 0.5f) continue;
-        const int x0 = std::max(0, std::min(w - 1, (int)std::floor(sx))), y0 = std::max(0, std::min(h - 1, (int)std::floor(sy)));
-        const int x1 = std::min(w - 1, x0 + 1), y1 = std::min(h - 1, y0 + 1);
-        const float ax = std::min(1.0f, std::max(0.0f, sx - x0)), ay = std::min(1.0f, std::max(0.0f, sy - y0));
-        const float v = (at(x0, y0) * (1 - ax) + at(x1, y0) * ax) * (1 - ay) + (at(x0, y1) * (1 - ax) + at(x1, y1) * ax) * ay;
-        const uint8_t g = (uint8_t)std::lround(std::min(255.0f, std::max(0.0f, (v - lo) * inv)));
+        const float sx = (cx + 0.5f - f.ox) * is - 0.5f;
+        if (sx < -0.5f || sx > w - 0.5f) continue;
+        const int x0 = std::max(0, std::min(w - 1, (int)std::floor(sx))), x1 = std::min(w - 1, x0 + 1);
+        const float ax = std::min(1.0f, std::max(0.0f, sx - x0));
+        const float top = v[(size_t)y0 * w + x0] * (1 - ax) + v[(size_t)y0 * w + x1] * ax;
+        const float bot = v[(size_t)y1 * w + x0] * (1 - ax) + v[(size_t)y1 * w + x1] * ax;
+        const uint8_t g = grey(top * (1 - ay) + bot * ay);
         uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
         px[0] = px[1] = px[2] = g;
       }
+    }
   }
  private:
   std::shared_ptr<ImageRenderer> me() { return std::static_pointer_cast<ImageRenderer>(shared_from_this()); }
@@ -501,12 +511,18 @@ class SegmentationRenderer : public Renderer {
     const uint8_t* lab = img->as<uint8_t>();
     const Fit f = fit(w, h, cw, ch);
     auto label_at = [&](int x, int y) -> int { return (x < 0 || y < 0 || x >= w || y >= h) ? 0 : lab[(size_t)y * w + x]; };
-    for (int cy = 0; cy < ch; ++cy)
+    std::vector<int> xs(cw);
+    for (int cx = 0; cx < cw; ++cx) xs[cx] = (int)std::floor((cx + 0.5f - f.ox) / f.scale);
+    for (int cy = 0; cy < ch; ++cy) {
+      const int y = (int)std::floor((cy + 0.5f - f.oy) / f.scale);
+      if (y < 0 || y >= h) continue;
+      const uint8_t* row = lab + (size_t)y * w;
       for (int cx = 0; cx < cw; ++cx) {
-        const int x = (int)std::floor((cx + 0.5f - f.ox) / f.scale), y = (int)std::floor((cy + 0.5f - f.oy) / f.scale);
-        const int l = label_at(x, y);
+        const int x = xs[cx];
+        if (x < 0 || x >= w || row[x] == 0) continue;
+        const int l = row[x];
         auto it = colors_.find(l);
-        if (l == 0 || it == colors_.end()) continue;
+        if (it == colors_.end()) continue;
         bool border = false;  // within borderRadius of a pixel with another label
         for (int b = -radius_; b <= radius_ && !border; ++b)
           for (int a = -radius_; a <= radius_ && !border; ++a)
@@ -514,8 +530,9 @@ class SegmentationRenderer : public Renderer {
         const float op = border ? borderOpacity_ : opacity_;
         uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
         const float c[3] = {it->second.r, it->second.g, it->second.b};
-        for (int k = 0; k < 3; ++k) px[k] = (uint8_t)std::lround(px[k] * (1 - op) + 255.0f * c[k] * op);
+        for (int k = 0; k < 3; ++k) px[k] = (uint8_t)(int)(px[k] * (1 - op) + 255.0f * c[k] * op + 0.5f);
       }
+    }
   }
  private:
   SegmentationRenderer(LabelColors c, float o, float bo, int r) : colors_(std::move(c)), opacity_(o), borderOpacity_(bo), radius_(r) {}
@@ -537,9 +554,9 @@ class RenderToImage : public ProcessObject {
   void evaluate() override {
     auto img = std::make_shared<Image>(w_, h_, TYPE_UINT8, 3);
     uint8_t* rgb = img->as<uint8_t>();
-    for (size_t i = 0; i < (size_t)w_ * h_; ++i) {
-      rgb[3 * i] = (uint8_t)std::lround(bg_.r * 255); rgb[3 * i + 1] = (uint8_t)std::lround(bg_.g * 255); rgb[3 * i + 2] = (uint8_t)std::lround(bg_.b * 255);
-    }
+    const uint8_t bg[3] = {(uint8_t)std::lround(bg_.r * 255), (uint8_t)std::lround(bg_.g * 255), (uint8_t)std::lround(bg_.b * 255)};
+    if (bg[0] == bg[1] && bg[1] == bg[2]) std::memset(rgb, bg[0], (size_t)w_ * h_ * 3);
+    else for (size_t i = 0; i < (size_t)w_ * h_; ++i) { rgb[3 * i] = bg[0]; rgb[3 * i + 1] = bg[1]; rgb[3 * i + 2] = bg[2]; }
     for (auto& r : renderers_) r->paint(rgb, w_, h_);
     output_ = img;
   }
