@@ -103,3 +103,20 @@ def test_reference_drivers_unchanged_on_the_shim(cohort, tmp_path, exe):
     img = np.asarray(Image.open(outdir / "PGBM-002" / "1-01_processed.jpg").convert("L"))
     area = (img > 100).sum() / 4.0      # 256x256 rendered into a 512x512 canvas
     assert abs(area - exp["dilated"].sum()) / max(exp["dilated"].sum(), 1) < 0.05
+
+
+def test_driver_shards_patients_over_all_visible_gpus(cohort, tmp_path):
+    """Contiguous patient ranges over every GPU of the box (one on the default test box); the masks must not
+    depend on the number of GPUs."""
+    import torch
+    n = torch.cuda.device_count()
+    root, base = cohort
+    out = tmp_path / "mg"
+    res = subprocess.run([DRIVER, "--data", str(base), "--out", str(out), "--dump-masks", "--no-export", "--gpus",
+                          ",".join(str(i) for i in range(n))], capture_output=True, text=True, check=True)
+    summary = json.loads(res.stdout.strip().splitlines()[-1])
+    assert summary["gpus"] == n and summary["ok"] == 15
+    host = _host_lib()
+    for p in range(3):
+        mask = np.fromfile(out / f"PGBM-{p + 1:03d}" / "1-02.mask", np.uint8).reshape(256, 256)
+        np.testing.assert_array_equal(mask, cm.o_pipeline(_phantom(host, 256, 256, p, 1))[1]["dilated"])

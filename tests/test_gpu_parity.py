@@ -272,3 +272,28 @@ def test_pipeline_size_independent_properties_full_c2(lib, ctx):
         lab, _ = ndi.label(pred)
         ids = {lab[y, x] for x, y in seeds if lab[y, x]}
         np.testing.assert_array_equal(a["rg_mask"][i], np.isin(lab, list(ids)).astype(np.uint8))
+
+
+# ---- re-entrancy: the reference runs 16 host threads through one device (main_parallel.cpp:336-343,401) ----
+def test_concurrent_host_threads_share_one_context(lib, ctx):
+    import threading
+    raws = [np.stack([cm.phantom(256 + 32 * (t % 3), 224, t, i) for i in range(3)]) for t in range(12)]
+    exp = [[cm.o_pipeline(r[i])[1]["dilated"] for i in range(3)] for r in raws]
+    got, errs = [None] * len(raws), []
+
+    def work(t):
+        try:
+            for _ in range(3):   # several rounds so that slots and scratch are reused across threads
+                got[t] = ctx.process_batch(raws[t], lib.default_params(), want=("dilated",))["dilated"].copy()
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(len(raws))]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for t in range(len(raws)):
+        for i in range(3):
+            np.testing.assert_array_equal(got[t][i], exp[t][i], err_msg=f"thread {t} slice {i}")
