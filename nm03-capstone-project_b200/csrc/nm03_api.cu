@@ -40,6 +40,7 @@ constexpr int kSlots = 4;
 
 const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
 const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); return e && e[0] == '1'; }();
+const bool g_no_dynamic = [] { const char* e = getenv("NM03_NO_DYNAMIC"); return e && e[0] == '1'; }();
 const bool g_no_skip = [] { const char* e = getenv("NM03_NO_SKIP"); return e && e[0] == '1'; }();  // A/B measurements
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
@@ -57,6 +58,8 @@ struct Slot {
   size_t stage_in_bytes = 0;
   void* stage_out = nullptr;      // scratch: device copy of outputs before D2H
   size_t stage_out_bytes = 0;
+  unsigned int* sched = nullptr;  // scratch: K1's work counters (zero between launches; the kernel resets them)
+  size_t sched_bytes = 0;
   float* lut = nullptr;           // scratch: f(key) table of K1 for the parameters in lut_key
   size_t lut_bytes = 0;
   float lut_key[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -200,6 +203,7 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
     }
   }
   k.lut = nullptr;
+  k.sched = nullptr;
   k.use_tma = g_no_tma ? 0 : 1;
   // clip floor shortcut: the largest key K with f(K) == f(lowest key); f must be non-decreasing in the
   // key (both normalisation factors of one sign) and the zero-border sentinel must not be in play
@@ -416,6 +420,11 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pred_bytes))) return rc;
   if (s->used && st != s->stream) CK(cudaStreamWaitEvent(st, s->done, 0));  // scratch reuse across streams
   if ((rc = ensure_lut(wk, s, st, pre))) return rc;
+  if (!s->sched) {
+    if ((rc = ensure(s, (void**)&s->sched, &s->sched_bytes, 2 * sizeof(unsigned int)))) return rc;
+    CK(cudaMemsetAsync(s->sched, 0, 2 * sizeof(unsigned int), st));
+  }
+  pre.sched = g_no_dynamic ? nullptr : s->sched;
   pre.in = d_slices;
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
@@ -628,6 +637,7 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.stage_in) cudaFree(s.stage_in);
       if (s.stage_out) cudaFree(s.stage_out);
       if (s.lut) cudaFree(s.lut);
+      if (s.sched) cudaFree(s.sched);
       if (s.done) cudaEventDestroy(s.done);
       if (s.stream) cudaStreamDestroy(s.stream);
     }

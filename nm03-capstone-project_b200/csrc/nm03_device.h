@@ -39,6 +39,7 @@ struct PreParams {
   float clip_min, clip_max;
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
+  unsigned int* sched;   // optional [2], zero between launches: work counter + finished-CTA counter of the persistent grid
   const float* lut;      // optional [65536]: f(key) for every 16-bit key (bit-identical to the arithmetic), else null
   // windows whose samples all have key <= skip_key map to f() == skip_val, so their median is known
   // without sorting (clip floor; 0 = off).  skip_key2 = the key replicated in both 16-bit halves.

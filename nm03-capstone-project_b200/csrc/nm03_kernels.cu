@@ -179,41 +179,65 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   extern __shared__ __align__(16) uint32_t smem_raw[];
   uint32_t* smem = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);  // TMA dst: 128 B
   uint32_t* P = smem;                                         // [PR][K1_PWS] packed keys (row q | row q+36 <<16)
-  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median); phase A: raw TMA tile
+  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median)
+
+  constexpr int RH = K1_MH + 2 * R;
+  constexpr int OFF = 8 - K1_HS_MAX - R;   // TMA box starts at x0-8 (16-byte rule): raw column col sits at box column col + OFF
+  static_assert(OFF >= 0 && RW + OFF <= K1_PWS, "halo does not fit the aligned TMA box");
+  uint16_t* T = reinterpret_cast<uint16_t*>(M + K1_MH * K1_MW);   // [RH][K1_PWS] raw samples of the NEXT work item (TMA destination)
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ int s_next;
 
   const int tid = threadIdx.x;
-  int slice, tile;
-  if (p.tile_order_on) { slice = blockIdx.x % p.n; tile = p.tile_order[blockIdx.x / p.n]; }
-  else { tile = blockIdx.x % (p.tiles_x * p.tiles_y); slice = blockIdx.x / (p.tiles_x * p.tiles_y); }
-  const int tx = tile % p.tiles_x, ty = tile / p.tiles_x;
-  const int x0 = tx * K1_TW, y0 = ty * K1_TH;
   const int w = p.w, h = p.h;
-  const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
   const uint32_t bias = p.input_unsigned ? 0x8000u : 0u;
+  const int total_blocks = p.n * p.tiles_x * p.tiles_y;
+  // work item `blk` -> (slice, tile origin); central tiles come first (see PreParams::tile_order)
+  auto decode = [&](int blk, int& slice_, int& x0_, int& y0_) {
+    int tile_;
+    if (p.tile_order_on) { slice_ = blk % p.n; tile_ = p.tile_order[blk / p.n]; }
+    else { tile_ = blk % (p.tiles_x * p.tiles_y); slice_ = blk / (p.tiles_x * p.tiles_y); }
+    x0_ = (tile_ % p.tiles_x) * K1_TW;
+    y0_ = (tile_ / p.tiles_x) * K1_TH;
+  };
+  // Persistent CTA.  Work items are handed out in launch order by an atomic counter (p.sched[0]), so
+  // the balance of the hardware block scheduler is kept while the raw tile of the NEXT item is fetched
+  // by TMA during the computation of the current one.  Without a counter (sched == null) items are
+  // taken with a fixed stride.
+  auto fetch = [&](int prev) -> int {   // one thread
+    return p.sched ? (int)atomicAdd(&p.sched[0], 1u) : prev + (int)gridDim.x;
+  };
+  auto issue_tma = [&](int blk) {       // one thread: bulk tensor copy of the raw halo tile of work item blk
+    int s_, x_, y_;
+    decode(blk, s_, x_, y_);
+    mbar_expect_tx(&bar, RH * K1_PWS * 2);
+    tma_load_3d(T, &tmap, &bar, x_ - 8, y_ - K1_HS_MAX - R, s_);
+  };
 
   // let a dependent kernel (K23, launched with programmatic serialization) be scheduled while this
   // grid drains; it still waits in cudaGridDependencySynchronize() until this grid has completed
   cudaTriggerProgrammaticLaunchCompletion();
 
+  if (tid == 0) {
+    if (p.use_tma) mbar_init(&bar, 1);
+    s_next = p.sched ? (int)atomicAdd(&p.sched[0], 1u) : (int)blockIdx.x;
+  }
+  __syncthreads();
+  int blk = s_next;
+  __syncthreads();   // s_next is rewritten inside the loop: everybody must have read the first value
+  if (p.use_tma && tid == 0 && blk < total_blocks) issue_tma(blk);
+
+  for (int iter = 0; blk < total_blocks; ++iter) {
+  int slice, x0, y0;
+  decode(blk, slice, x0, y0);
+  const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
+
   // ---- phase A: raw halo tile -> packed keys --------------------------------------------------
   const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
   if (p.use_tma) {
-    // One bulk tensor copy brings the (MH+2R) x 144 int16 halo tile into shared memory (the float
-    // median tile's storage is free until phase B); rows/columns outside the image arrive as zeros.
-    // Without swizzle the innermost start coordinate must be a multiple of 16 bytes, so the box starts
-    // at x0-8 and raw column `col` of the tile sits at box column col + OFF.
-    constexpr int RH = K1_MH + 2 * R;
-    constexpr int OFF = 8 - K1_HS_MAX - R;
-    static_assert(OFF >= 0 && RW + OFF <= K1_PWS, "halo does not fit the aligned TMA box");
-    __shared__ __align__(8) uint64_t bar;
-    uint16_t* T = reinterpret_cast<uint16_t*>(M);   // [RH][K1_PWS] raw samples
-    if (tid == 0) mbar_init(&bar, 1);
-    __syncthreads();
-    if (tid == 0) {
-      mbar_expect_tx(&bar, RH * K1_PWS * 2);
-      tma_load_3d(T, &tmap, &bar, x0 - 8, gy0, slice);
-    }
-    mbar_wait(&bar, 0);
+    // The (MH+2R) x 144 int16 halo tile arrives in shared memory by one bulk tensor copy; rows/columns
+    // outside the image arrive as zeros.
+    mbar_wait(&bar, iter & 1);
     const bool interior = gx0 >= 0 && gy0 >= 0 && gx0 + RW <= w && gy0 + RH <= h;
     if (!p.border_zero) {
       // 4 packed words per thread: pixels i..i+3 of row q (low halves) and of row q+36 (high halves);
@@ -282,7 +306,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       P[idx] = a | (b << 16);
     }
   }
+  if (tid == 0) s_next = fetch(blk);   // the previous value of s_next was read by everybody before the last barrier
   __syncthreads();
+  const int next_blk = s_next;
+  if (p.use_tma && tid == 0 && next_blk < total_blocks) issue_tma(next_blk);  // T is free again
 
   // ---- phase B: median of the K x K window on packed keys, then f() ---------------------------
   // Work items (packed row, run of 8 columns).  An item whose whole input footprint lies at or below
@@ -500,6 +527,14 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       }
     }
   }
+  __syncthreads();   // everybody is done with this item (and has read s_next) before the next one starts
+  blk = next_blk;
+  }  // persistent loop over work items
+  // the last CTA to leave resets the work counter for the next launch that uses it
+  if (p.sched && tid == 0) {
+    __threadfence();
+    if (atomicAdd(&p.sched[1], 1u) == gridDim.x - 1) { p.sched[0] = 0u; p.sched[1] = 0u; __threadfence(); }
+  }
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
@@ -520,8 +555,7 @@ static EncodeTiledFn encode_tiled_fn() {
 // tensor map over the [n][h][w] 16-bit batch with a (144, MH+2R, 1) box; false if TMA cannot be used
 static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
   if ((p.w & 7) || ((uintptr_t)p.in & 15) || !encode_tiled_fn()) return false;
-  static_assert((size_t)K1_MH * K1_MW * 4 >= (size_t)(K1_MH + 6) * K1_PWS * 2, "raw tile must fit in the median tile storage");
-  const cuuint64_t dims[3] = {(cuuint64_t)p.w, (cuuint64_t)p.h, (cuuint64_t)p.n};
+    const cuuint64_t dims[3] = {(cuuint64_t)p.w, (cuuint64_t)p.h, (cuuint64_t)p.n};
   const cuuint64_t strides[2] = {(cuuint64_t)p.w * 2, (cuuint64_t)p.w * p.h * 2};
   const cuuint32_t box[3] = {(cuuint32_t)K1_PWS, (cuuint32_t)(K1_MH + 2 * R), 1};
   const cuuint32_t estr[3] = {1, 1, 1};
@@ -533,12 +567,19 @@ static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
 template <int K, int HS, int MODE>
 static cudaError_t launch_k1m(const PreParams& p0, cudaStream_t s) {
   constexpr int R = K / 2;
-  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + 128;
+  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 128;
   PreParams p = p0;
   CUtensorMap map;
   memset(&map, 0, sizeof(map));
   p.use_tma = p0.use_tma && make_tmap(p, R, &map);
-  const int grid = p.n * p.tiles_x * p.tiles_y;
+  // persistent grid: at most one CTA per resident slot (K1_MIN_CTAS per SM), each loops over work items
+  static int sm_count[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && sm_count[dev] == 0) cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+  const int slots = K1_MIN_CTAS * ((dev >= 0 && dev < 64 && sm_count[dev] > 0) ? sm_count[dev] : 148);
+  const int total = p.n * p.tiles_x * p.tiles_y;
+  const int grid = total < slots ? total : slots;
   k1_preprocess<K, HS, MODE><<<grid, K1_THREADS, smem, s>>>(p, map);
   return cudaGetLastError();
 }
@@ -553,7 +594,7 @@ static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
-  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + 128);
+  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 128);
   cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess && HS > 2)
