@@ -115,12 +115,18 @@ class Net:
         self.ops = new_ops
         return self
 
-    def emit_cuda(self, outputs, in_names, out_names, indent="  ", prefix="t"):
+    def emit_cuda(self, outputs, in_names, out_names, indent="  ", prefix="t", order="build"):
         live = self.live_ops(outputs)
         name = {i: n for i, n in enumerate(in_names)}
         lines = []
         fn = {"min": "NM03_MIN", "max": "NM03_MAX", "min3": "NM03_MIN3", "max3": "NM03_MAX3"}
-        for idx, op in enumerate(self.ops):
+        seq = list(enumerate(self.ops))
+        if order == "level":   # as-soon-as-possible levels: maximal instruction-level parallelism in source order
+            depth = {}
+            for idx, op in seq:
+                depth[self.n_in + idx] = 1 + max([depth.get(a, 0) for a in op[1:]])
+            seq.sort(key=lambda t: (depth[self.n_in + t[0]], t[0]))
+        for idx, op in seq:
             vid = self.n_in + idx
             if vid not in live:
                 continue
@@ -373,6 +379,7 @@ def check_run(net, raw, outs, R, k, trials=3000):
 
 
 RUN = 8  # outputs per thread-run (packed registers: 16 pixels)
+ORDER = "build"
 
 
 def emit(args):
@@ -393,7 +400,7 @@ def emit(args):
               f"aligned blocks <= {maxlen} columns at offset {blk_off}")
         print(f"#define NM03_MEDIAN_RUN_{k}(v, o) do {{ \\")
         in_names = [f"(v)[{c}][{r}]" for c in range(RUN + k - 1) for r in range(k)]
-        body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(RUN)], indent="  ", prefix=f"m{k}_")
+        body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(RUN)], indent="  ", prefix=f"m{k}_", order=ORDER)
         for ln in body.split("\n"):
             print(ln + " \\")
         print("} while (0)")
@@ -424,8 +431,10 @@ if __name__ == "__main__":
     ap.add_argument("--emit", action="store_true")
     ap.add_argument("--report", action="store_true")
     ap.add_argument("--run", type=int, default=RUN, help="outputs per thread-run")
+    ap.add_argument("--order", default="build", choices=["build", "level"], help="emission order of the operations")
     a = ap.parse_args()
     RUN = a.run
+    ORDER = a.order
     if a.emit:
         emit(a)
     else:
