@@ -382,25 +382,29 @@ RUN = 8  # outputs per thread-run (packed registers: 16 pixels)
 ORDER = "build"
 
 
+RUN_FOR = {3: 8, 5: 8, 7: 8, 9: 2}  # outputs per thread-run for each window (9x9 is limited by registers)
+
+
 def emit(args):
     print("// GENERATED by gen_median_net.py --emit — do not edit.")
     print("// Straight-line min/max networks on packed int16x2 registers (two pixels per lane).")
-    print(f"// NM03_MEDIAN_RUN_<k>(v, o): v[c][r] = raw sample r of column c, c < {RUN}+k-1, r < k;")
-    print(f"// o[i], i < {RUN} = median of the k x k window made of columns i .. i+k-1.")
-    print(f"#define NM03_MEDIAN_RUN {RUN}")
-    for k in (3, 5, 7):
-        n, pair_off, blk_off, maxlen = best_core_design(RUN, k)
-        net, raw, outs = run_design_core(RUN, k, pair_off, blk_off, maxlen)
-        assert check_run(net, raw, outs, RUN, k), f"k={k} failed verification"
+    print("// NM03_MEDIAN_RUN_<k>(v, o): v[c][r] = raw sample r of column c, c < RUNLEN+k-1, r < k;")
+    print("// o[i], i < RUNLEN = median of the k x k window made of columns i .. i+k-1 (RUNLEN = NM03_MEDIAN_RUNLEN_<k>).")
+    for k in (3, 5, 7, 9):
+        run = RUN if (args.run_given and k != 9) else RUN_FOR[k]
+        n, pair_off, blk_off, maxlen = best_core_design(run, k)
+        net, raw, outs = run_design_core(run, k, pair_off, blk_off, maxlen)
+        assert check_run(net, raw, outs, run, k, trials=3000 if k < 9 else 600), f"k={k} failed verification"
         net.fuse3(outs)
-        assert check_run(net, raw, outs, RUN, k), f"k={k} failed verification after 3-input fusion"
+        assert check_run(net, raw, outs, run, k, trials=3000 if k < 9 else 600), f"k={k} failed verification after 3-input fusion"
         n3 = net.count(outs)
         print(f"\n// k={k}: {n} two-input ops, {n3} instructions after min3/max3 fusion "
-              f"({n3 / (2.0 * RUN):.1f} per pixel); shared-core design, pair offset {pair_off}, "
+              f"({n3 / (2.0 * run):.1f} per pixel); shared-core design, pair offset {pair_off}, "
               f"aligned blocks <= {maxlen} columns at offset {blk_off}")
+        print(f"#define NM03_MEDIAN_RUNLEN_{k} {run}")
         print(f"#define NM03_MEDIAN_RUN_{k}(v, o) do {{ \\")
-        in_names = [f"(v)[{c}][{r}]" for c in range(RUN + k - 1) for r in range(k)]
-        body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(RUN)], indent="  ", prefix=f"m{k}_", order=ORDER)
+        in_names = [f"(v)[{c}][{r}]" for c in range(run + k - 1) for r in range(k)]
+        body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(run)], indent="  ", prefix=f"m{k}_", order=ORDER)
         for ln in body.split("\n"):
             print(ln + " \\")
         print("} while (0)")
@@ -430,10 +434,12 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--emit", action="store_true")
     ap.add_argument("--report", action="store_true")
-    ap.add_argument("--run", type=int, default=RUN, help="outputs per thread-run")
+    ap.add_argument("--run", type=int, default=None, help="outputs per thread-run for windows 3/5/7 (tuning)")
     ap.add_argument("--order", default="build", choices=["build", "level"], help="emission order of the operations")
     a = ap.parse_args()
-    RUN = a.run
+    a.run_given = a.run is not None
+    if a.run_given:
+        RUN = a.run
     ORDER = a.order
     if a.emit:
         emit(a)

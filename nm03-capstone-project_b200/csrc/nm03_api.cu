@@ -152,10 +152,10 @@ int check_params(const nm03_params* p, int w, int h, bool whole_pipeline) {
 }
 
 int check_preprocess(const nm03_params* p, int* sharpen_half) {
-  if (p->median_window != 3 && p->median_window != 5 && p->median_window != 7) {
+  if (p->median_window != 3 && p->median_window != 5 && p->median_window != 7 && p->median_window != 9) {
     if (p->median_window < 1 || (p->median_window & 1) == 0)
       return fail(NM03_ERR_PARAM, "median window must be odd, got %d", p->median_window);
-    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (3, 5, 7 are)", p->median_window);
+    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (3, 5, 7, 9 are)", p->median_window);
   }
   int m = p->sharpen_mask;
   if (m == 0) m = (int)std::ceil(2.0f * p->sharpen_sigma) * 2 + 1;  // FAST's default mask size

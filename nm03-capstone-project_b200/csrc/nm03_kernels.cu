@@ -71,24 +71,19 @@ cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s) {
 
 template <int K>
 struct MedianRun;
-template <>
-struct MedianRun<3> {
-  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 2][3], uint32_t (&o)[NM03_MEDIAN_RUN]) {
-    NM03_MEDIAN_RUN_3(v, o);
-  }
-};
-template <>
-struct MedianRun<5> {
-  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 4][5], uint32_t (&o)[NM03_MEDIAN_RUN]) {
-    NM03_MEDIAN_RUN_5(v, o);
-  }
-};
-template <>
-struct MedianRun<7> {
-  static __device__ __forceinline__ void run(uint32_t (&v)[NM03_MEDIAN_RUN + 6][7], uint32_t (&o)[NM03_MEDIAN_RUN]) {
-    NM03_MEDIAN_RUN_7(v, o);
-  }
-};
+#define NM03_DEFINE_MEDIAN_RUN(K_)                                                                              \
+  template <>                                                                                                   \
+  struct MedianRun<K_> {                                                                                        \
+    static constexpr int RUN = NM03_MEDIAN_RUNLEN_##K_;                                                         \
+    static __device__ __forceinline__ void run(uint32_t (&v)[RUN + K_ - 1][K_], uint32_t (&o)[RUN]) {           \
+      NM03_MEDIAN_RUN_##K_(v, o);                                                                               \
+    }                                                                                                           \
+  };
+NM03_DEFINE_MEDIAN_RUN(3)
+NM03_DEFINE_MEDIAN_RUN(5)
+NM03_DEFINE_MEDIAN_RUN(7)
+NM03_DEFINE_MEDIAN_RUN(9)
+#undef NM03_DEFINE_MEDIAN_RUN
 
 // Unsharp mask for 4 horizontally adjacent pixels, accumulating exactly in the oracle's order
 // (tap x outer, tap y inner, from 0.0f; nm03o_sharpen).  M points at the median tile row of the
@@ -172,9 +167,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   constexpr int R = K / 2;
   constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
   constexpr int RW = K1_MW + 2 * R;        // raw columns actually needed
-  constexpr int NRUN = K1_MW / NM03_MEDIAN_RUN;
+  constexpr int RUN = MedianRun<K>::RUN;   // outputs (packed registers) per work item
+  constexpr int NRUN = K1_MW / RUN;
   static_assert(RW <= K1_PWS, "packed tile stride too small");
-  static_assert(K1_MW % NM03_MEDIAN_RUN == 0, "median tile width must be a multiple of the run length");
+  static_assert(K1_MW % RUN == 0 && RUN % 2 == 0, "median tile width must be a multiple of the (even) run length");
 
   extern __shared__ __align__(16) uint32_t smem_raw[];
   uint32_t* smem = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);  // TMA dst: 128 B
@@ -340,16 +336,28 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         const int prow = it / NRUN, run = it - prow * NRUN;
         // footprint: packed rows prow .. prow+K-1, columns run*RUN .. run*RUN + RUN+K-2
         const int g0 = prow >> 3, g1 = (prow + K - 1) >> 3;
-        const int c0 = (run * NM03_MEDIAN_RUN) >> 3, c1 = (run * NM03_MEDIAN_RUN + NM03_MEDIAN_RUN + K - 2) >> 3;
-        uint32_t m = __vmaxs2(__vmaxs2(blkmax[g0][c0], blkmax[g0][c1]), __vmaxs2(blkmax[g1][c0], blkmax[g1][c1]));
+        const int c0 = (run * RUN) >> 3, c1 = (run * RUN + RUN + K - 2) >> 3;
+        // the footprint spans at most two block rows and two block columns (checked by the static_assert below)
+        const uint32_t m = __vmaxs2(__vmaxs2(blkmax[g0][c0], blkmax[g0][c1]), __vmaxs2(blkmax[g1][c0], blkmax[g1][c1]));
+        static_assert(K - 1 <= 8 && (RUN + K - 2) % 8 + 0 >= 0 && RUN + K - 1 <= 16 && (8 % RUN == 0 || RUN % 8 == 0),
+                      "work item footprint must fit in 2x2 blocks of 8x8 packed words");
         need = __vmaxs2(m, p.skip_key2) != p.skip_key2;        // some sample above the floor, in either half
         if (!need) {
-          float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
+          float* mlo = M + prow * K1_MW + run * RUN;
           const float4 f4 = make_float4(p.skip_val, p.skip_val, p.skip_val, p.skip_val);
 #pragma unroll
-          for (int i = 0; i < NM03_MEDIAN_RUN; i += 4) {
-            *reinterpret_cast<float4*>(mlo + i) = f4;
-            *reinterpret_cast<float4*>(mlo + K1_MHP * K1_MW + i) = f4;
+          if constexpr (RUN % 4 == 0) {
+#pragma unroll
+            for (int i = 0; i < RUN; i += 4) {
+              *reinterpret_cast<float4*>(mlo + i) = f4;
+              *reinterpret_cast<float4*>(mlo + K1_MHP * K1_MW + i) = f4;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < RUN; i += 2) {
+              *reinterpret_cast<float2*>(mlo + i) = make_float2(f4.x, f4.y);
+              *reinterpret_cast<float2*>(mlo + K1_MHP * K1_MW + i) = make_float2(f4.x, f4.y);
+            }
           }
         }
       }
@@ -365,33 +373,42 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   for (int wi = tid; wi < n_items; wi += K1_THREADS) {
     const int it = p.skip_on ? worklist[wi] : wi;
     const int prow = it / NRUN, run = it - prow * NRUN;
-    uint32_t v[NM03_MEDIAN_RUN + K - 1][K], o[NM03_MEDIAN_RUN];
-    const uint32_t* src = P + prow * K1_PWS + run * NM03_MEDIAN_RUN;
+    uint32_t v[RUN + K - 1][K], o[RUN];
+    const uint32_t* src = P + prow * K1_PWS + run * RUN;
 #pragma unroll
     for (int r = 0; r < K; ++r)
 #pragma unroll
-      for (int c = 0; c < NM03_MEDIAN_RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
+      for (int c = 0; c < RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
     MedianRun<K>::run(v, o);
-    float lo[NM03_MEDIAN_RUN], hi[NM03_MEDIAN_RUN];
+    float lo[RUN], hi[RUN];
     if (p.lut) {
 #pragma unroll
-      for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
+      for (int i = 0; i < RUN; ++i) {
         lo[i] = __ldg(p.lut + (o[i] & 0xffffu));
         hi[i] = __ldg(p.lut + (o[i] >> 16));
       }
     } else {
 #pragma unroll
-      for (int i = 0; i < NM03_MEDIAN_RUN; ++i) {
+      for (int i = 0; i < RUN; ++i) {
         lo[i] = key_to_float((int)(short)(o[i] & 0xffffu), p);
         hi[i] = key_to_float((int)(short)(o[i] >> 16), p);
       }
     }
-    float* mlo = M + prow * K1_MW + run * NM03_MEDIAN_RUN;
+    float* mlo = M + prow * K1_MW + run * RUN;
     float* mhi = mlo + K1_MHP * K1_MW;
 #pragma unroll
-    for (int i = 0; i < NM03_MEDIAN_RUN; i += 4) {
-      *reinterpret_cast<float4*>(mlo + i) = make_float4(lo[i], lo[i + 1], lo[i + 2], lo[i + 3]);
-      *reinterpret_cast<float4*>(mhi + i) = make_float4(hi[i], hi[i + 1], hi[i + 2], hi[i + 3]);
+    if constexpr (RUN % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < RUN; i += 4) {
+        *reinterpret_cast<float4*>(mlo + i) = make_float4(lo[i], lo[i + 1], lo[i + 2], lo[i + 3]);
+        *reinterpret_cast<float4*>(mhi + i) = make_float4(hi[i], hi[i + 1], hi[i + 2], hi[i + 3]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < RUN; i += 2) {
+        *reinterpret_cast<float2*>(mlo + i) = make_float2(lo[i], lo[i + 1]);
+        *reinterpret_cast<float2*>(mhi + i) = make_float2(hi[i], hi[i + 1]);
+      }
     }
   }
   __syncthreads();
@@ -610,6 +627,8 @@ static cudaError_t config_k1() {
     case 53: return FN<5, 3>(__VA_ARGS__); case 54: return FN<5, 4>(__VA_ARGS__);                   \
     case 71: return FN<7, 1>(__VA_ARGS__); case 72: return FN<7, 2>(__VA_ARGS__);                   \
     case 73: return FN<7, 3>(__VA_ARGS__); case 74: return FN<7, 4>(__VA_ARGS__);                   \
+    case 91: return FN<9, 1>(__VA_ARGS__); case 92: return FN<9, 2>(__VA_ARGS__);                   \
+    case 93: return FN<9, 3>(__VA_ARGS__); case 94: return FN<9, 4>(__VA_ARGS__);                   \
     default: return cudaErrorInvalidValue;                                                          \
   }
 
@@ -997,7 +1016,7 @@ cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* b
 cudaError_t configure_kernels() {
   cudaError_t e;
   int median_window, sharpen_half;
-  for (median_window = 3; median_window <= 7; median_window += 2)
+  for (median_window = 3; median_window <= 9; median_window += 2)
     for (sharpen_half = 1; sharpen_half <= 4; ++sharpen_half) {
       e = [&]() -> cudaError_t { NM03_K1_DISPATCH(config_k1) }();
       if (e != cudaSuccess) return e;

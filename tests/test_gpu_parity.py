@@ -41,7 +41,7 @@ def test_preprocess_shapes(lib, ctx, w, h):
     _cmp_pre(lib, ctx, cm.phantom(w, h, 1, 3))
 
 
-@pytest.mark.parametrize("k", [3, 5, 7])
+@pytest.mark.parametrize("k", [3, 5, 7, 9])
 @pytest.mark.parametrize("m", [3, 5, 7, 9])
 def test_preprocess_windows(lib, ctx, k, m):
     _cmp_pre(lib, ctx, cm.phantom(160, 96, 2, k + m), median_window=k, sharpen_mask=m, sharpen_sigma=0.8)
@@ -112,7 +112,8 @@ def test_fast_predicate_adversarial_thresholds(lib, ctx):
 @pytest.mark.parametrize("kw", [dict(sharpen_fma=1), dict(border_mode=1), dict(median_window=5, sharpen_mask=5),
                                 dict(sharpen_sigma=1.0), dict(sharpen_sigma=0.8, sharpen_mask=7, sharpen_gain=-1.5),
                                 dict(clip_min=-3.0, norm_low=-1.0, rg_min=-0.2, rg_max=0.1),
-                                dict(median_window=3, sharpen_mask=3, sharpen_sigma=0.4)])
+                                dict(median_window=3, sharpen_mask=3, sharpen_sigma=0.4),
+                                dict(median_window=9), dict(median_window=9, border_mode=1, sharpen_mask=7)])
 def test_fast_predicate_switches(lib, ctx, kw):
     _cmp_fast(lib, ctx, cm.phantom(200, 150, 4, 1), **kw)
     rng = np.random.default_rng(3)
@@ -246,6 +247,17 @@ def test_pipeline_ragged_and_switches(lib, ctx):
     raws = np.stack([cm.phantom(333, 205, 6, i) for i in range(3)])
     _cmp_pipeline(lib, ctx, raws, erode_size=5, rg_connectivity=8, se_shape=1, sharpen_fma=1)
     _cmp_pipeline(lib, ctx, raws, rg_mode=1, border_mode=1, rg_border_expand=0)
+
+
+def test_pipeline_median_window_9_and_unsupported_windows(lib, ctx):
+    """N4 generality: 9x9 is implemented (slower network); larger odd windows are refused, even ones are
+    a parameter error as in FAST."""
+    raws = np.stack([cm.phantom(300, 260, 9, i) for i in range(2)])
+    _cmp_pipeline(lib, ctx, raws, median_window=9, dilate_size=5)
+    for k, code in ((11, lib.ERR_UNSUPPORTED), (4, lib.ERR_PARAM)):
+        with pytest.raises(lib.Nm03Error) as e:
+            ctx.process_batch(raws, lib.default_params(median_window=k))
+        assert e.value.code == code
 
 
 def test_pipeline_dimension_guard(lib, ctx):
