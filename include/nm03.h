@@ -36,7 +36,7 @@ typedef enum nm03_status {
   NM03_ERR_NO_SEEDS = -4,      /* SeededRegionGrowing without seed points */
   NM03_ERR_SEED_OOB = -5,      /* seed point outside the image */
   NM03_ERR_UNSUPPORTED = -6,   /* valid in FAST, not implemented here (stated in the message) */
-  NM03_ERR_TOO_LARGE = -7,     /* slice exceeds what one thread-block cluster can keep on chip */
+  NM03_ERR_TOO_LARGE = -7,     /* batch or slice exceeds a fixed capacity (built-in scratch of the _noalloc entry point; rows too wide for the band fallback) */
   NM03_ERR_CUDA = -8,          /* CUDA runtime error (message has the detail) */
   NM03_ERR_NO_DEVICE = -9,
   NM03_ERR_NOMEM = -10

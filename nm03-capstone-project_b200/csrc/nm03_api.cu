@@ -42,6 +42,7 @@ const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[
 const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); return e && e[0] == '1'; }();
 const bool g_no_dynamic = [] { const char* e = getenv("NM03_NO_DYNAMIC"); return e && e[0] == '1'; }();
 const bool g_no_skip = [] { const char* e = getenv("NM03_NO_SKIP"); return e && e[0] == '1'; }();  // A/B measurements
+const bool g_force_global = [] { const char* e = getenv("NM03_FORCE_GLOBAL_FILL"); return e && e[0] == '1'; }();  // tests
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
@@ -56,6 +57,11 @@ struct Slot {
   size_t pred_bytes = 0;
   void* stage_in = nullptr;       // scratch: device copy of host inputs
   size_t stage_in_bytes = 0;
+  uint32_t* gmask = nullptr;      // scratch: bit-packed mask of the global-memory fill fallback
+  size_t gmask_bytes = 0;
+  int* dflag = nullptr;           // scratch: device "changed" flag of that fallback
+  size_t dflag_bytes = 0;
+  int* hflag = nullptr;           // pinned host copy of the flag
   void* stage_out = nullptr;      // scratch: device copy of outputs before D2H
   size_t stage_out_bytes = 0;
   unsigned int* sched = nullptr;  // scratch: K1's work counters (zero between launches; the kernel resets them)
@@ -326,8 +332,15 @@ int pick_cluster(int n, int h, int wpr, int* rows_per) {
   int c = 1;
   for (;; c *= 2) {
     const int rows = (h + c - 1) / c;
-    if (nm03::seg_smem_bytes(rows, wpr) <= cap) break;
-    if (c == nm03::SEG_MAX_CLUSTER) return fail(NM03_ERR_TOO_LARGE, "slice of %d rows x %d words exceeds cluster capacity", h, wpr);
+    if (!g_force_global && nm03::seg_smem_bytes(rows, wpr) <= cap) break;
+    if (c == nm03::SEG_MAX_CLUSTER || g_force_global) {
+      // beyond what 8 CTAs can hold: the global-memory fallback works on bands of rows
+      int band = g_force_global ? 64 : 512;
+      while (band >= 16 && nm03::seg_smem_bytes(band, wpr) > cap) band /= 2;
+      if (band < 16) return fail(NM03_ERR_TOO_LARGE, "image rows of %d words are too wide for the band fallback", wpr);
+      *rows_per = band < h ? band : h;
+      return 0;
+    }
   }
   while (c < nm03::SEG_MAX_CLUSTER && n * c * 2 <= 148 && (h + 2 * c - 1) / (2 * c) >= 32) c *= 2;
   if (g_force_cluster > 0) {  // NM03_CLUSTER: tuning override (must still fit)
@@ -382,6 +395,42 @@ int get_worker(nm03_ctx* ctx, int gpu, Worker** wk) {
   if (gpu < 0 || gpu >= (int)ctx->workers.size())
     return fail(NM03_ERR_INVALID, "gpu index %d out of range (context has %zu)", gpu, ctx->workers.size());
   *wk = ctx->workers[gpu];
+  return NM03_OK;
+}
+
+// K23 for `seg` on stream st: one cluster launch, or — for slices beyond cluster capacity — band-wise
+// fill launches repeated until the device flag stays clear (this path waits for the stream)
+int run_segment(Worker* wk, Slot* s, cudaStream_t st, const nm03::SegParams& seg) {
+  if (seg.cluster > 0) {
+    CK(nm03::launch_segment(seg, st));
+    wk->launches += 1;
+    return NM03_OK;
+  }
+  int rc;
+  const size_t bytes = (size_t)seg.n * seg.h * seg.wpr * 4;
+  if ((rc = ensure(s, (void**)&s->gmask, &s->gmask_bytes, bytes))) return rc;
+  if ((rc = ensure(s, (void**)&s->dflag, &s->dflag_bytes, sizeof(int)))) return rc;
+  if (!s->hflag) {
+    cudaError_t e = cudaHostAlloc((void**)&s->hflag, sizeof(int), cudaHostAllocPortable);
+    if (e != cudaSuccess) return fail(NM03_ERR_NOMEM, "cudaHostAlloc failed: %s", cudaGetErrorString(e));
+  }
+  int passes = 0;
+  if (seg.do_fill) {
+    const int nbands = (seg.h + seg.rows_per - 1) / seg.rows_per;
+    for (;; ++passes) {
+      CK(cudaMemsetAsync(s->dflag, 0, sizeof(int), st));
+      CK(nm03::launch_band_fill(seg, s->gmask, s->dflag, passes == 0, st));
+      wk->launches += 1;
+      CK(cudaMemcpyAsync(s->hflag, s->dflag, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      if (passes > 0 && *s->hflag == 0) { ++passes; break; }
+      if (passes > 4 * (nbands + seg.wpr) * 64) return fail(NM03_ERR_CUDA, "region growing did not converge");
+    }
+  } else {
+    CK(cudaMemcpyAsync(s->gmask, seg.pred, bytes, cudaMemcpyDeviceToDevice, st));
+  }
+  CK(nm03::launch_global_morph(seg, s->gmask, passes, st));
+  wk->launches += 1;
   return NM03_OK;
 }
 
@@ -445,13 +494,13 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   seg.eroded = (p->erode_size > 0) ? d_out->eroded : nullptr;
   seg.rg_mask = d_out->rg_mask;
   seg.iterations = d_out->rg_iterations;
-  CK(nm03::launch_segment(seg, st));
+  if ((rc = run_segment(wk, s, st, seg))) return rc;
   if (prof) {
     CK(cudaEventRecord(rec.e[2], st));
     std::lock_guard<std::mutex> lk(wk->prof_mu);
     wk->prof_pending.push_back(rec);
   }
-  wk->launches += 2;
+  wk->launches += 1;
   CK(cudaEventRecord(s->done, st));
   s->used = true;
   return NM03_OK;
@@ -525,6 +574,9 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
     if ((rc = se_halfwidths(params->erode_size, params->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
   }
   DeviceGuard g(wk->device);
+  if (seg.cluster == 0)
+    return fail(NM03_ERR_TOO_LARGE, "slice %dx%d exceeds one cluster's shared memory; the fallback for such slices needs scratch "
+                "memory and is only available through nm03_process_batch_device", w, h);
   uint32_t* scratch = nullptr;
   if ((rc = noalloc_scratch(wk->device, &scratch))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
@@ -638,6 +690,9 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.stage_out) cudaFree(s.stage_out);
       if (s.lut) cudaFree(s.lut);
       if (s.sched) cudaFree(s.sched);
+      if (s.gmask) cudaFree(s.gmask);
+      if (s.dflag) cudaFree(s.dflag);
+      if (s.hflag) cudaFreeHost(s.hflag);
       if (s.done) cudaEventDestroy(s.done);
       if (s.stream) cudaStreamDestroy(s.stream);
     }
@@ -854,8 +909,8 @@ int nm03_region_grow(nm03_ctx* ctx, int gpu, const float* image, int w, int h, c
   seg.pred = s->pred;
   seg.rg_mask = (uint8_t*)s->stage_out;
   seg.iterations = (int32_t*)((uint8_t*)s->stage_out + ((npx + 3) & ~(size_t)3));
-  CK(nm03::launch_segment(seg, s->stream));
-  wk->launches += 2;
+  if ((rc = run_segment(wk, s, s->stream, seg))) return rc;
+  wk->launches += 1;
   CK(cudaMemcpyAsync(mask, seg.rg_mask, npx, cudaMemcpyDeviceToHost, s->stream));
   int it = 0;
   CK(cudaMemcpyAsync(&it, seg.iterations, 4, cudaMemcpyDeviceToHost, s->stream));
@@ -893,8 +948,8 @@ int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, i
   seg.pred = s->pred;
   if (op == NM03_MORPH_DILATE) seg.dilated = (uint8_t*)s->stage_out;
   else seg.eroded = (uint8_t*)s->stage_out;
-  CK(nm03::launch_segment(seg, s->stream));
-  wk->launches += 2;
+  if ((rc = run_segment(wk, s, s->stream, seg))) return rc;
+  wk->launches += 1;
   CK(cudaMemcpyAsync(out, s->stage_out, npx, cudaMemcpyDeviceToHost, s->stream));
   CK(cudaEventRecord(s->done, s->stream));
   s->used = true;

@@ -74,7 +74,7 @@ struct SegParams {
   uint8_t* rg_mask;      // optional
   int32_t* iterations;   // optional [n]
   int w, h, n, wpr;
-  int cluster;           // CTAs per slice
+  int cluster;           // CTAs per slice; 0 = the slice exceeds cluster capacity: global-memory fallback, rows_per = band height
   int rows_per;          // rows owned by one CTA
   int seg_rows;          // rows swept by one thread per pass
   int do_fill, conn8, border_expand, host_mode;
@@ -90,6 +90,9 @@ size_t seg_smem_bytes(int rows_per, int wpr);
 // launchers (return cudaError_t of the launch)
 cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, int mode, cudaStream_t s);
 cudaError_t launch_segment(const SegParams& p, cudaStream_t s);
+// global-memory fallback (SegParams::cluster == 0): band-wise fill pass over the bit-packed mask, then morphology
+cudaError_t launch_band_fill(const SegParams& p, uint32_t* gmask, int* gflag, int first_launch, cudaStream_t s);
+cudaError_t launch_global_morph(const SegParams& p, const uint32_t* gmask, int passes, cudaStream_t s);
 cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float lo, float hi, uint32_t* bits,
                                   cudaStream_t s);
 cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* bits, cudaStream_t s);

@@ -942,6 +942,138 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
 #undef MROW
 }
 
+// ---- global-memory fallback for slices that exceed one cluster's shared memory ------------------------
+// The mask lives bit-packed in global memory.  One CTA takes a band of rows, loads it (plus one halo
+// row each side) into shared memory, grows it to its local fixed point with the same sweep passes as
+// K23, and writes it back; information crosses a band boundary once per launch.  The host relaunches
+// until a launch reports no change through the global flag.
+__global__ void __launch_bounds__(SEG_THREADS, 1) k2_band_fill(const __grid_constant__ SegParams p, uint32_t* __restrict__ gmask,
+                                                               int* __restrict__ gflag, int first_launch) {
+  extern __shared__ __align__(16) uint32_t smem[];
+  const int wpr = p.wpr, rows = p.rows_per;
+  const int nbands = (p.h + rows - 1) / rows;
+  const int slice = blockIdx.x / nbands, band = blockIdx.x - slice * nbands;
+  const int tid = threadIdx.x;
+  uint32_t* Pp = smem;
+  uint32_t* Mm = smem + (size_t)rows * wpr;
+  const int nseg_max = (rows + p.seg_rows - 1) / p.seg_rows;
+  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * wpr);
+  uint8_t* act1 = act0 + (size_t)nseg_max * wpr;
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+  const int y_begin = band * rows;
+  const int nrows = min(rows, p.h - y_begin);
+  const uint32_t* gp = p.pred + (size_t)slice * p.h * wpr;
+  uint32_t* gm = gmask + (size_t)slice * p.h * wpr;
+  const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
+  for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  for (int i = tid; i < 2 * nseg_max * wpr; i += SEG_THREADS) act0[i] = 1;   // everything is looked at once per launch
+  __syncthreads();
+  for (int i = tid; i < rows * wpr; i += SEG_THREADS) {
+    const int r = i / wpr, k = i - r * wpr;
+    uint32_t v = r < nrows ? gp[(size_t)(y_begin + r) * wpr + k] : 0u;
+    if (k == wpr - 1) v &= lastmask;
+    Pp[i] = v;
+    if (!first_launch && r < nrows) MROW(r)[k] = gm[(size_t)(y_begin + r) * wpr + k];
+  }
+  if (!first_launch)
+    for (int k = tid; k < 2 * wpr; k += SEG_THREADS) {   // halo rows written by the neighbouring bands in earlier launches
+      const int side = k / wpr, kk = k - side * wpr;
+      const int y = side == 0 ? y_begin - 1 : y_begin + nrows;
+      if (y >= 0 && y < p.h) MROW(side == 0 ? -1 : nrows)[kk] = gm[(size_t)y * wpr + kk];
+    }
+  __syncthreads();
+  if (first_launch) {
+    for (int i = tid; i < p.n_seeds; i += SEG_THREADS) {
+      const int sx = p.seeds[i].x, sy = p.seeds[i].y;
+      if (!p.host_mode) {
+        const int r = sy - y_begin;
+        if (r >= 0 && r < nrows) atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
+      } else {
+        const int ddx[8] = {0, 1, -1, 0, 1, -1, 1, -1}, ddy[8] = {1, 0, 0, -1, 1, 1, -1, -1};
+        for (int d = 0; d < (p.conn8 ? 8 : 4); ++d) {
+          const int nx = sx + ddx[d], ny = sy + ddy[d];
+          const int r = ny - y_begin;
+          if (nx < 0 || nx >= p.w || r < 0 || r >= nrows) continue;
+          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * wpr + (nx >> 5)]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const bool masked = !p.border_expand && !p.host_mode;
+  int ever = first_launch;   // the seeds themselves are a change
+  for (int q = 0;; ++q) {
+    uint8_t* an = (q & 1) ? act1 : act0;
+    uint8_t* ax = (q & 1) ? act0 : act1;
+    int changed;
+    if (p.conn8) changed = masked ? fill_pass<true, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<true, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
+    else changed = masked ? fill_pass<false, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<false, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
+    changed = __syncthreads_or(changed);
+    if (!changed) break;
+    ever = 1;
+  }
+  if (ever && !first_launch && tid == 0) *gflag = 1;
+  if (first_launch && tid == 0) *gflag = 1;           // a second launch always runs so that the halos are seen once
+  for (int i = tid; i < nrows * wpr; i += SEG_THREADS) {
+    const int r = i / wpr, k = i - r * wpr;
+    gm[(size_t)(y_begin + r) * wpr + k] = MROW(r)[k];
+  }
+#undef MROW
+}
+
+// cast + dilation / erosion from the global bit-packed mask (same row-run form as in K23)
+__global__ void k3_global_morph(const __grid_constant__ SegParams p, const uint32_t* __restrict__ gmask, int passes) {
+  const int wpr = p.wpr;
+  const long long total = (long long)p.n * p.h * wpr;
+  const bool vec = (p.w & 15) == 0 && ((((size_t)p.dilated) | ((size_t)p.eroded) | ((size_t)p.rg_mask)) & 15) == 0;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % wpr);
+    const long long row = i / wpr;
+    const int y = (int)(row % p.h), slice = (int)(row / p.h);
+    if (p.iterations && k == 0 && y == 0) p.iterations[slice] = passes;
+    const uint32_t* gm = gmask + (size_t)slice * p.h * wpr;
+    auto word = [&](int yy, int kk) -> uint32_t { return (yy < 0 || yy >= p.h || kk < 0 || kk >= wpr) ? 0u : gm[(size_t)yy * wpr + kk]; };
+    const size_t rowoff = ((size_t)slice * p.h + y) * p.w;
+    const uint32_t m = word(y, k);
+    if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
+    if (p.dilated) {
+      uint32_t acc = p.dil_n > 0 ? 0u : m;
+      for (int b = -p.dil_n; b <= p.dil_n && p.dil_n > 0; ++b) {
+        if (y + b < 0 || y + b >= p.h) continue;
+        const uint32_t c = word(y + b, k), l = word(y + b, k - 1), rr = word(y + b, k + 1);
+        const int hw = p.dil_hw[b + p.dil_n];
+        acc |= c;
+        for (int s2 = 1; s2 <= hw; ++s2) acc |= __funnelshift_r(c, rr, s2) | __funnelshift_l(l, c, s2);
+      }
+      store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+    }
+    if (p.eroded) {
+      uint32_t acc = m;
+      for (int b = -p.ero_n; b <= p.ero_n && p.ero_n > 0 && acc; ++b) {
+        if (y + b < 0 || y + b >= p.h) { acc = 0u; break; }
+        const uint32_t c = word(y + b, k), l = word(y + b, k - 1), rr = word(y + b, k + 1);
+        const int hw = p.ero_hw[b + p.ero_n];
+        acc &= c;
+        for (int s2 = 1; s2 <= hw; ++s2) acc &= __funnelshift_r(c, rr, s2) & __funnelshift_l(l, c, s2);
+      }
+      store_word_u8(p.eroded + rowoff, k * 32, p.w, acc, vec);
+    }
+  }
+}
+
+cudaError_t launch_band_fill(const SegParams& p, uint32_t* gmask, int* gflag, int first_launch, cudaStream_t s) {
+  const int nbands = (p.h + p.rows_per - 1) / p.rows_per;
+  k2_band_fill<<<p.n * nbands, SEG_THREADS, seg_smem_bytes(p.rows_per, p.wpr), s>>>(p, gmask, gflag, first_launch);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_global_morph(const SegParams& p, const uint32_t* gmask, int passes, cudaStream_t s) {
+  const long long total = (long long)p.n * p.h * p.wpr;
+  long long g = (total + 255) / 256;
+  k3_global_morph<<<(int)(g > 148 * 8 ? 148 * 8 : (g < 1 ? 1 : g)), 256, 0, s>>>(p, gmask, passes);
+  return cudaGetLastError();
+}
+
 size_t seg_smem_bytes(int rows_per, int wpr) {
   // predicate + mask planes, plus two activity-flag arrays (at most one byte per row and word column)
   return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * wpr * 4 + 2 * (size_t)rows_per * wpr;
@@ -1022,6 +1154,8 @@ cudaError_t configure_kernels() {
       if (e != cudaSuccess) return e;
     }
   e = cudaFuncSetAttribute(k23_segment, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 64);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(k2_band_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 64);
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(k23_segment, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
 }
