@@ -43,6 +43,7 @@ const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); 
 const bool g_no_dynamic = [] { const char* e = getenv("NM03_NO_DYNAMIC"); return e && e[0] == '1'; }();
 const bool g_no_skip = [] { const char* e = getenv("NM03_NO_SKIP"); return e && e[0] == '1'; }();  // A/B measurements
 const bool g_force_global = [] { const char* e = getenv("NM03_FORCE_GLOBAL_FILL"); return e && e[0] == '1'; }();  // tests
+const int g_seg_rows = [] { const char* e = getenv("NM03_SEG_ROWS"); return e ? atoi(e) : 0; }();
 const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return e ? atoi(e) : 0; }();
 
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
@@ -361,7 +362,8 @@ int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, cons
   k.cluster = c;
   k.rows_per = rows;
   int seg = (rows * k.wpr + nm03::SEG_THREADS - 1) / nm03::SEG_THREADS;
-  k.seg_rows = seg < 4 ? 4 : seg;
+  k.seg_rows = seg < 4 ? 4 : (seg > 16 ? 16 : seg);   // 8-16 rows per sweep measured best (tools/k_time.py)
+  if (g_seg_rows > 0) k.seg_rows = g_seg_rows;   // NM03_SEG_ROWS: tuning override
   k.do_fill = do_fill;
   if (do_fill) {
     if (p->rg_connectivity != 4 && p->rg_connectivity != 8)
