@@ -488,7 +488,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     // fast value lies within the proven error bound of a threshold is redone exactly.
     constexpr int HE = MODE == K1_FAST_HE2 ? 2 : HS;
     constexpr int NT = 2 * HE + 1;
-    constexpr int RB = 8;                       // output rows per thread
+    constexpr int RB = (HE > 2) ? 4 : 8;        // output rows per thread (fewer with the wide kernel: registers)
     for (int it = tid; it < (K1_TH / RB) * (K1_TW / 4); it += K1_THREADS) {
       const int band = it / (K1_TW / 4), xq = it - band * (K1_TW / 4);
       const int oyl0 = band * RB;
