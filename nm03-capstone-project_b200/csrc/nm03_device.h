@@ -62,7 +62,10 @@ struct PreParams {
 enum { K1_EXACT = 0, K1_FAST_FULL = 1, K1_FAST_HE2 = 2 };  // sharpen evaluation mode
 
 // ---- K2+K3: flood fill + morphology on bit-packed planes, one thread-block cluster per slice ----
-constexpr int SEG_THREADS = 256;
+#ifndef NM03_SEG_THREADS
+#define NM03_SEG_THREADS 256
+#endif
+constexpr int SEG_THREADS = NM03_SEG_THREADS;
 constexpr int SEG_HALO = 7;            // rows of the neighbouring CTA's mask kept for the SE (size <= 15)
 constexpr int SEG_MAX_SEEDS = 512;
 constexpr int SEG_MAX_CLUSTER = 8;

@@ -669,6 +669,11 @@ __device__ __forceinline__ void store_word_u8(uint8_t* __restrict__ row, int x, 
 // read from shared memory as they are (chaotic relaxation of a monotone operator: any interleaving
 // converges to the same fixed point, and a pass without any change proves it has been reached).
 // MASKED = image-border pixels may be labelled but never act as sources (rg_border_expand = 0).
+// Rows of both bit planes are stored with an ODD stride in shared memory, so a warp whose lanes walk
+// along the words of a row and a warp whose lanes walk down the rows of one word column are both
+// free of bank conflicts.
+__host__ __device__ inline int seg_row_stride(int wpr) { return wpr | 1; }
+
 // Activity flags: an item (row segment x word column) is processed in a pass only if it, or one of
 // the items it reads from, changed since it was last looked at; a changing item wakes itself and its
 // neighbours for the next pass.  Work is therefore proportional to the grown region, not to the image.
@@ -676,8 +681,8 @@ template <bool CONN8, bool MASKED>
 __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32_t* __restrict__ Pp,
                                          const SegParams& p, int nrows, int y_begin, int tid,
                                          uint8_t* __restrict__ act_now, uint8_t* __restrict__ act_next) {
-  const int wpr = p.wpr;
-#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+  const int wpr = p.wpr, ws = seg_row_stride(p.wpr);
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * ws)
   const int lastk = (p.w - 1) >> 5;
   const uint32_t lastbit = 1u << ((p.w - 1) & 31);
   int changed = 0;
@@ -717,10 +722,10 @@ __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32
       // software pipeline: rows r-step (behind), r (here), r+step (ahead) live in registers and the
       // row after that is fetched while this one is computed, so a step's critical path is ALU only
       Row3 behind = load_row(r - step), here = load_row(r), ahead = load_row(r + step);
-      uint32_t pw = Pp[r * wpr + k];
+      uint32_t pw = Pp[r * ws + k];
       for (int cnt = ra; cnt < rb; ++cnt, r += step) {
         const Row3 next = load_row(r + 2 * step);   // rows up to +-2 outside the segment exist (halo >= 2)
-        const uint32_t pw_next = (cnt + 1 < rb) ? Pp[(r + step) * wpr + k] : 0u;
+        const uint32_t pw_next = (cnt + 1 < rb) ? Pp[(r + step) * ws + k] : 0u;
         const uint32_t m = here.c;
         uint32_t vs = behind.s | ahead.s;
         if (CONN8) vs |= (vs << 1) | (vs >> 1) | ((behind.l | ahead.l) >> 31) | ((behind.r | ahead.r) << 31);
@@ -764,24 +769,24 @@ __device__ __forceinline__ int fill_pass(uint32_t* __restrict__ Mm, const uint32
 __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_constant__ SegParams p) {
   cg::cluster_group cluster = cg::this_cluster();
   extern __shared__ __align__(16) uint32_t smem[];
-  const int wpr = p.wpr, rows = p.rows_per, C = p.cluster;
+  const int wpr = p.wpr, ws = seg_row_stride(p.wpr), rows = p.rows_per, C = p.cluster;
   const int rank = C > 1 ? (int)cluster.block_rank() : 0;
   const int slice = blockIdx.x / C;
   const int tid = threadIdx.x;
   // planes: predicate rows owned by this CTA; mask rows with SEG_HALO halo rows above and below
   uint32_t* Pp = smem;                                   // [rows][wpr]
-  uint32_t* Mm = smem + (size_t)rows * wpr;              // [rows + 2*HALO][wpr]
+  uint32_t* Mm = smem + (size_t)rows * ws;               // [rows + 2*HALO][ws]  (ws = odd row stride)
   const int nseg_max = (rows + p.seg_rows - 1) / p.seg_rows;
-  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * wpr);  // [nseg][wpr] x 2
+  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * ws);   // [nseg][wpr] x 2
   uint8_t* act1 = act0 + (size_t)nseg_max * wpr;
   __shared__ int s_flag[3];                              // rotating "somebody changed" flags (see below)
-#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * ws)
   const int y_begin = rank * rows;                       // first image row owned
   const int nrows = max(0, min(rows, p.h - y_begin));    // rows actually inside the image
   const uint32_t* gp = p.pred + (size_t)slice * p.h * wpr;
   const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
 
-  for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  for (int i = tid; i < (rows + 2 * SEG_HALO) * ws; i += SEG_THREADS) Mm[i] = 0u;
   for (int i = tid; i < 2 * nseg_max * wpr; i += SEG_THREADS) act0[i] = 0;
   // Launched with programmatic stream serialization: everything above overlaps the tail of the kernel
   // that produces the predicate plane; its memory is only touched after this point.
@@ -790,7 +795,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
     const int r = i / wpr, k = i - r * wpr;
     uint32_t v = r < nrows ? __ldcg(gp + (size_t)(y_begin + r) * wpr + k) : 0u;
     if (k == wpr - 1) v &= lastmask;
-    Pp[i] = v;
+    Pp[r * ws + k] = v;
   }
   if (tid < 3) s_flag[tid] = 0;
   __syncthreads();
@@ -798,13 +803,20 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   int passes = 0;
   if (p.do_fill) {
     // ---- seeds ------------------------------------------------------------------------------
+    // a seed is a change nobody has looked at yet: wake its item AND the items around it (the growth
+    // may start in a neighbouring segment or word column although the seed's own item stays as it is)
+    auto wake = [&](int r, int k) {
+      const int nsg = (nrows + p.seg_rows - 1) / p.seg_rows, sg = r / p.seg_rows;
+      for (int a = max(0, sg - 1); a <= min(nsg - 1, sg + 1); ++a)
+        for (int b = max(0, k - 1); b <= min(wpr - 1, k + 1); ++b) act0[a * wpr + b] = 1;
+    };
     for (int i = tid; i < p.n_seeds; i += SEG_THREADS) {
       const int sx = p.seeds[i].x, sy = p.seeds[i].y;
       if (!p.host_mode) {
         const int r = sy - y_begin;
         if (r >= 0 && r < nrows) {
-          atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
-          act0[(r / p.seg_rows) * wpr + (sx >> 5)] = 1;
+          atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * ws + (sx >> 5)]);
+          wake(r, sx >> 5);
         }
       } else {
         // FAST executeOnHost: the seed's neighbours are tested, not the seed itself
@@ -813,8 +825,8 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
           const int nx = sx + ddx[d], ny = sy + ddy[d];
           const int r = ny - y_begin;
           if (nx < 0 || nx >= p.w || r < 0 || r >= nrows) continue;
-          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * wpr + (nx >> 5)]);
-          act0[(r / p.seg_rows) * wpr + (nx >> 5)] = 1;
+          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * ws + (nx >> 5)]);
+          wake(r, nx >> 5);
         }
       }
     }
@@ -835,7 +847,9 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
       uint8_t* ax = (q & 1) ? act0 : act1;
       if (p.conn8) changed = masked ? fill_pass<true, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<true, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
       else changed = masked ? fill_pass<false, true>(Mm, Pp, p, nrows, y_begin, tid, an, ax) : fill_pass<false, false>(Mm, Pp, p, nrows, y_begin, tid, an, ax);
-      changed = __syncthreads_or(changed | hchg);
+      // the seeds themselves are progress the neighbouring CTAs have not seen: the first round always
+      // continues, so that every halo row is refreshed (and its readers woken) at least once
+      changed = __syncthreads_or(changed | hchg) | (q == 0 && C > 1);
       if (C == 1) {
         if (!changed) break;
         continue;
@@ -852,7 +866,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
         const int nb = side == 0 ? rank - 1 : rank + 1;
         if (nb < 0 || nb >= C) continue;
         const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
-        const uint32_t v = remote[(size_t)((side == 0 ? rows - 1 : 0) + SEG_HALO) * wpr + kk];
+        const uint32_t v = remote[(size_t)((side == 0 ? rows - 1 : 0) + SEG_HALO) * ws + kk];
         uint32_t* mine = MROW(side == 0 ? -1 : rows) + kk;
         if (*mine != v) {
           *mine = v;
@@ -870,7 +884,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
       __syncthreads();
     }
   } else {
-    for (int i = tid; i < rows * wpr; i += SEG_THREADS) MROW(0)[i] = Pp[i];
+    for (int i = tid; i < rows * wpr; i += SEG_THREADS) { const int r = i / wpr, k = i - r * wpr; MROW(r)[k] = Pp[r * ws + k]; }
     __syncthreads();
   }
   if (p.iterations && rank == 0 && tid == 0) p.iterations[slice] = passes;
@@ -885,8 +899,8 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
       const int nb = side == 0 ? rank - 1 : rank + 1;
       if (nb < 0 || nb >= C) continue;
       const uint32_t* remote = cluster.map_shared_rank(Mm, nb);
-      if (side == 0) MROW(-1 - hr)[kk] = remote[(size_t)(rows - 1 - hr + SEG_HALO) * wpr + kk];
-      else MROW(rows + hr)[kk] = remote[(size_t)(hr + SEG_HALO) * wpr + kk];
+      if (side == 0) MROW(-1 - hr)[kk] = remote[(size_t)(rows - 1 - hr + SEG_HALO) * ws + kk];
+      else MROW(rows + hr)[kk] = remote[(size_t)(hr + SEG_HALO) * ws + kk];
     }
     cluster.sync();  // nobody exits (or overwrites) while a neighbour still reads its rows
   } else {
@@ -950,29 +964,29 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
 __global__ void __launch_bounds__(SEG_THREADS, 1) k2_band_fill(const __grid_constant__ SegParams p, uint32_t* __restrict__ gmask,
                                                                int* __restrict__ gflag, int first_launch) {
   extern __shared__ __align__(16) uint32_t smem[];
-  const int wpr = p.wpr, rows = p.rows_per;
+  const int wpr = p.wpr, ws = seg_row_stride(p.wpr), rows = p.rows_per;
   const int nbands = (p.h + rows - 1) / rows;
   const int slice = blockIdx.x / nbands, band = blockIdx.x - slice * nbands;
   const int tid = threadIdx.x;
   uint32_t* Pp = smem;
-  uint32_t* Mm = smem + (size_t)rows * wpr;
+  uint32_t* Mm = smem + (size_t)rows * ws;
   const int nseg_max = (rows + p.seg_rows - 1) / p.seg_rows;
-  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * wpr);
+  uint8_t* act0 = reinterpret_cast<uint8_t*>(Mm + (size_t)(rows + 2 * SEG_HALO) * ws);
   uint8_t* act1 = act0 + (size_t)nseg_max * wpr;
-#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * wpr)
+#define MROW(r) (Mm + (size_t)((r) + SEG_HALO) * ws)
   const int y_begin = band * rows;
   const int nrows = min(rows, p.h - y_begin);
   const uint32_t* gp = p.pred + (size_t)slice * p.h * wpr;
   uint32_t* gm = gmask + (size_t)slice * p.h * wpr;
   const uint32_t lastmask = (p.w & 31) ? ((1u << (p.w & 31)) - 1u) : 0xffffffffu;
-  for (int i = tid; i < (rows + 2 * SEG_HALO) * wpr; i += SEG_THREADS) Mm[i] = 0u;
+  for (int i = tid; i < (rows + 2 * SEG_HALO) * ws; i += SEG_THREADS) Mm[i] = 0u;
   for (int i = tid; i < 2 * nseg_max * wpr; i += SEG_THREADS) act0[i] = 1;   // everything is looked at once per launch
   __syncthreads();
   for (int i = tid; i < rows * wpr; i += SEG_THREADS) {
     const int r = i / wpr, k = i - r * wpr;
     uint32_t v = r < nrows ? gp[(size_t)(y_begin + r) * wpr + k] : 0u;
     if (k == wpr - 1) v &= lastmask;
-    Pp[i] = v;
+    Pp[r * ws + k] = v;
     if (!first_launch && r < nrows) MROW(r)[k] = gm[(size_t)(y_begin + r) * wpr + k];
   }
   if (!first_launch)
@@ -987,14 +1001,14 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k2_band_fill(const __grid_cons
       const int sx = p.seeds[i].x, sy = p.seeds[i].y;
       if (!p.host_mode) {
         const int r = sy - y_begin;
-        if (r >= 0 && r < nrows) atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * wpr + (sx >> 5)]);
+        if (r >= 0 && r < nrows) atomicOr(&MROW(r)[sx >> 5], (1u << (sx & 31)) & Pp[r * ws + (sx >> 5)]);
       } else {
         const int ddx[8] = {0, 1, -1, 0, 1, -1, 1, -1}, ddy[8] = {1, 0, 0, -1, 1, 1, -1, -1};
         for (int d = 0; d < (p.conn8 ? 8 : 4); ++d) {
           const int nx = sx + ddx[d], ny = sy + ddy[d];
           const int r = ny - y_begin;
           if (nx < 0 || nx >= p.w || r < 0 || r >= nrows) continue;
-          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * wpr + (nx >> 5)]);
+          atomicOr(&MROW(r)[nx >> 5], (1u << (nx & 31)) & Pp[r * ws + (nx >> 5)]);
         }
       }
     }
@@ -1075,8 +1089,8 @@ cudaError_t launch_global_morph(const SegParams& p, const uint32_t* gmask, int p
 }
 
 size_t seg_smem_bytes(int rows_per, int wpr) {
-  // predicate + mask planes, plus two activity-flag arrays (at most one byte per row and word column)
-  return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * wpr * 4 + 2 * (size_t)rows_per * wpr;
+  // predicate + mask planes (odd row stride), plus two activity-flag arrays (at most one byte per row and word column)
+  return ((size_t)rows_per + (size_t)rows_per + 2 * SEG_HALO) * seg_row_stride(wpr) * 4 + 2 * (size_t)rows_per * wpr;
 }
 
 cudaError_t launch_segment(const SegParams& p, cudaStream_t s) {

@@ -309,3 +309,25 @@ def test_concurrent_host_threads_share_one_context(lib, ctx):
     for t in range(len(raws)):
         for i in range(3):
             np.testing.assert_array_equal(got[t][i], exp[t][i], err_msg=f"thread {t} slice {i}")
+
+
+@pytest.mark.parametrize("w,h", [(100, 290), (512, 512), (300, 1024)])
+@pytest.mark.parametrize("conn", [4, 8])
+def test_region_grow_from_a_seed_next_to_every_internal_boundary(lib, ctx, w, h, conn):
+    """Regression (found by the property test): growth that starts exactly across a row-segment, word-column
+    or CTA boundary from the seed.  One-pixel-wide lines, the seed walked along them pixel by pixel."""
+    vert = np.zeros((h, w), np.float32)
+    vert[20:h - 20, 46] = 0.8
+    horiz = np.zeros((h, w), np.float32)
+    horiz[h // 2 + 1, 5:w - 5] = 0.8
+    diag = np.zeros((h, w), np.float32)
+    n = min(w, h) - 10
+    diag[np.arange(5, 5 + n), np.arange(5, 5 + n)] = 0.8
+    p = lib.default_params(rg_connectivity=conn)
+    for img, seeds in ((vert, [(46, y) for y in list(range(20, 60)) + list(range(h // 2 - 20, h // 2 + 20))]),
+                       (horiz, [(x, h // 2 + 1) for x in range(25, 70)]),
+                       (diag, [(5 + i, 5 + i) for i in range(20, 75)])):
+        for sx, sy in seeds:
+            got, _ = ctx.region_grow(img, np.array([[sx, sy]], np.int32), p)
+            rc, exp, _ = cm.o_region_grow(img, 0.74, 0.91, [[sx, sy]], conn=conn)
+            assert np.array_equal(got, exp), f"seed ({sx},{sy}) conn {conn}: got {int(got.sum())} px, expected {int(exp.sum())}"

@@ -7,6 +7,9 @@ from hypothesis import strategies as st
 
 import common as cm
 
+import os
+
+GPU_EXAMPLES = int(os.environ.get("NM03_HYP_EXAMPLES", "40"))   # raise for soak runs
 SETTINGS = dict(deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
 
 
@@ -56,24 +59,46 @@ def test_oracle_fill_and_morphology_properties(seed, conn, size):
 
 
 @pytest.mark.gpu
-@settings(max_examples=30, **SETTINGS)
+@settings(max_examples=GPU_EXAMPLES, **SETTINGS)
 @given(seed=st.integers(0, 2**31), w=st.integers(100, 330), h=st.integers(100, 290),
        k=st.sampled_from([3, 5, 7, 9]), m=st.sampled_from([3, 5, 7, 9]), sigma=st.sampled_from([0.4, 0.5, 0.8, 1.2]),
        conn=st.sampled_from([4, 8]), dil=st.sampled_from([3, 5, 9]), ero=st.sampled_from([0, 3, 7]),
-       kind=st.sampled_from(["phantom", "full", "ties", "window", "blocks"]), fma=st.booleans(), want_float=st.booleans())
-def test_cuda_pipeline_matches_oracle_on_random_cases(lib, seed, w, h, k, m, sigma, conn, dil, ero, kind, fma, want_float):
+       kind=st.sampled_from(["phantom", "full", "ties", "window", "blocks"]), fma=st.booleans(), want_float=st.booleans(),
+       rg_mode=st.sampled_from([0, 0, 1]), border_expand=st.sampled_from([1, 1, 0]), se=st.sampled_from([0, 0, 1]),
+       nslices=st.sampled_from([1, 1, 3]))
+def test_cuda_pipeline_matches_oracle_on_random_cases(lib, seed, w, h, k, m, sigma, conn, dil, ero, kind, fma, want_float,
+                                                      rg_mode, border_expand, se, nslices):
     rng = np.random.default_rng(seed)
-    raw = _random_image(rng, w, h, kind)
+    raws = np.stack([_random_image(rng, w, h, kind) for _ in range(nslices)])
     kw = dict(median_window=k, sharpen_mask=m, sharpen_sigma=sigma, rg_connectivity=conn, dilate_size=dil, erode_size=ero,
-              sharpen_fma=int(fma))
+              sharpen_fma=int(fma), rg_mode=rg_mode, rg_border_expand=border_expand, se_shape=se)
     want = ("dilated", "rg_mask") + (("eroded",) if ero else ()) + (("sharpened", "median") if want_float else ())
     global _CTX
     try:
         _CTX
     except NameError:
         _CTX = lib.Context([0])
-    res = _CTX.process_batch(raw[None], lib.default_params(**kw), want=want)
-    rc, exp = cm.o_pipeline(raw, cm.oparams(**kw))
-    assert rc == 0
-    for name in want:
-        np.testing.assert_array_equal(res[name][0], exp[name], err_msg=name)
+    res = _CTX.process_batch(raws, lib.default_params(**kw), want=want)
+    for i in range(nslices):
+        rc, exp = cm.o_pipeline(raws[i], cm.oparams(**kw))
+        assert rc == 0
+        for name in want:
+            np.testing.assert_array_equal(res[name][i], exp[name], err_msg=f"slice {i} {name}")
+
+
+@pytest.mark.gpu
+@settings(max_examples=max(8, GPU_EXAMPLES // 4), **SETTINGS)
+@given(seed=st.integers(0, 2**31), w=st.integers(331, 700), h=st.integers(291, 1100), conn=st.sampled_from([4, 8]),
+       kind=st.sampled_from(["phantom", "window", "blocks"]), border_expand=st.sampled_from([1, 0]), nslices=st.sampled_from([1, 2, 5]))
+def test_cuda_pipeline_matches_oracle_on_larger_random_slices(lib, seed, w, h, conn, kind, border_expand, nslices):
+    """Larger slices exercise other cluster sizes / row splits of the flood fill (default windows, masks only)."""
+    rng = np.random.default_rng(seed)
+    raws = np.stack([_random_image(rng, w, h, kind) for _ in range(nslices)])
+    kw = dict(rg_connectivity=conn, rg_border_expand=border_expand, erode_size=3)
+    with lib.Context([0]) as ctx:
+        res = ctx.process_batch(raws, lib.default_params(**kw), want=("dilated", "rg_mask", "eroded"))
+    for i in range(nslices):
+        rc, exp = cm.o_pipeline(raws[i], cm.oparams(**kw))
+        assert rc == 0
+        for name in ("rg_mask", "dilated", "eroded"):
+            np.testing.assert_array_equal(res[name][i], exp[name], err_msg=f"slice {i} {name}")
