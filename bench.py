@@ -176,14 +176,14 @@ def driver_io_figure():
         return None
     try:
         with tempfile.TemporaryDirectory() as td:
-            subprocess.check_call([drv, "--make-dataset", td + "/d", "--patients", "4", "--slices", str(SLICES), "--size", str(W)],
+            subprocess.check_call([drv, "--make-dataset", td + "/d", "--patients", "20", "--slices", str(SLICES), "--size", str(W)],
                                   stdout=subprocess.DEVNULL)
             out = {}
             for name, extra in (("dicom_to_mask", ["--no-export"]), ("dicom_to_jpeg", [])):
                 r = subprocess.run([drv, "--data", td + "/d", "--out", td + "/o", "--gpus", "0"] + extra, capture_output=True,
                                    text=True, timeout=300)
                 out[name + "_slices_per_sec"] = json.loads(r.stdout.strip().splitlines()[-1])["slices_per_sec"]
-            out["sample"] = f"4 patients x {SLICES} slices {W}x{H}, DICOM files in a temp dir, includes context start-up"
+            out["sample"] = f"20 patients x {SLICES} slices {W}x{H} (BASELINE configs[2]), DICOM files in a temp dir, timed after context start-up"
             return out
     except Exception as e:  # informational only
         return {"error": str(e)[:200]}

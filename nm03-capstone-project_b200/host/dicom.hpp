@@ -9,6 +9,12 @@
 #pragma once
 #include <cstdint>
 #include <cstring>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+
 #include <fstream>
 #include <stdexcept>
 #include <string>
@@ -89,14 +95,26 @@ inline std::string str_value(const Cursor& c, const Element& e) {
 
 }  // namespace detail
 
-// Parse a Part-10 file image held in memory.
-inline Slice parse(const uint8_t* data, size_t size) {
+// Header of a slice plus the location of its pixel data inside the file image (no pixel copy).
+struct View {
+  int rows = 0, cols = 0, bits_allocated = 0, pixel_representation = 0, instance_number = 0;
+  double rescale_slope = 1.0, rescale_intercept = 0.0;
+  size_t pixel_offset = 0, pixel_bytes = 0;
+};
+
+// Scan a Part-10 file image.  `data` holds the first `size` bytes of a file of `total` bytes (total = 0: the
+// whole file is in memory): the header must lie inside `data`, the pixel payload only inside the file.
+// Throws NeedMore if the header does not fit in `size` bytes.
+struct NeedMore : std::runtime_error { NeedMore() : std::runtime_error("DICOM: header longer than the bytes read") {} };
+
+inline View parse_view(const uint8_t* data, size_t size, size_t total = 0) {
   using namespace detail;
+  if (total < size) total = size;
+  const bool partial = total > size;
   Cursor c{data, size};
   if (size < 132 || std::memcmp(data + 128, "DICM", 4) != 0) throw std::runtime_error("DICOM: missing DICM preamble");
   c.off = 132;
-  std::string ts = "1.2.840.10008.1.2";  // default: implicit VR little endian
-  // file meta information: always explicit VR little endian, group 0002
+  std::string ts = "1.2.840.10008.1.2";
   while (c.has(8)) {
     const size_t save = c.off;
     Element e = read_header(c, true);
@@ -109,10 +127,8 @@ inline Slice parse(const uint8_t* data, size_t size) {
   if (ts == "1.2.840.10008.1.2") explicit_vr = false;
   else if (ts == "1.2.840.10008.1.2.1") explicit_vr = true;
   else throw std::runtime_error("DICOM: unsupported transfer syntax " + ts + " (only uncompressed little endian)");
-
-  Slice s;
+  View s;
   int samples = 1, frames = 1;
-  bool have_pixels = false;
   while (c.has(8)) {
     Element e = read_header(c, explicit_vr);
     if (e.len == 0xFFFFFFFFu) {
@@ -120,7 +136,11 @@ inline Slice parse(const uint8_t* data, size_t size) {
       skip_undefined(c, explicit_vr, false);
       continue;
     }
-    if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated element");
+    const bool is_pixels = e.group == 0x7FE0 && e.elem == 0x0010;
+    if (is_pixels ? e.value_off + (size_t)e.len > total : !c.has(e.len)) {
+      if (partial && !is_pixels) throw NeedMore();
+      throw std::runtime_error("DICOM: truncated element");
+    }
     const uint8_t* v = c.p + e.value_off;
     auto us = [&]() { return e.len >= 2 ? (int)(v[0] | (v[1] << 8)) : 0; };
     if (e.group == 0x0028) {
@@ -144,16 +164,72 @@ inline Slice parse(const uint8_t* data, size_t size) {
       if (frames > 1) throw std::runtime_error("DICOM: multi-frame images are not supported");
       const size_t need = (size_t)s.rows * s.cols * 2;
       if (e.len < need) throw std::runtime_error("DICOM: pixel data shorter than rows*cols");
-      s.pixels.resize((size_t)s.rows * s.cols);
-      std::memcpy(s.pixels.data(), v, need);  // little endian host assumed (x86-64 / aarch64)
-      have_pixels = true;
+      s.pixel_offset = e.value_off;
+      s.pixel_bytes = need;
+      return s;
     }
     c.off += e.len;
-    if (have_pixels) break;
   }
-  if (!have_pixels) throw std::runtime_error("DICOM: no pixel data element");
+  if (partial) throw NeedMore();
+  throw std::runtime_error("DICOM: no pixel data element");
+}
+
+// Parse a Part-10 file image held in memory (header + a copy of the pixels).
+inline Slice parse(const uint8_t* data, size_t size) {
+  const View v = parse_view(data, size);
+  Slice s;
+  s.rows = v.rows; s.cols = v.cols; s.bits_allocated = v.bits_allocated; s.pixel_representation = v.pixel_representation;
+  s.rescale_slope = v.rescale_slope; s.rescale_intercept = v.rescale_intercept; s.instance_number = v.instance_number;
+  s.pixels.resize((size_t)v.rows * v.cols);
+  std::memcpy(s.pixels.data(), data + v.pixel_offset, v.pixel_bytes);  // little endian host assumed (x86-64 / aarch64)
   return s;
 }
+
+// Positional reads of one file: the feeder reads the first bytes, parses the header there, and then
+// reads the pixel payload straight into pinned staging memory (one copy, kernel -> pinned).
+class FileReader {
+ public:
+  FileReader() = default;
+  explicit FileReader(const std::string& path) {
+    fd_ = ::open(path.c_str(), O_RDONLY);
+    if (fd_ < 0) throw std::runtime_error("cannot open " + path);
+    struct stat st;
+    if (::fstat(fd_, &st) != 0 || st.st_size <= 0) { ::close(fd_); fd_ = -1; throw std::runtime_error("cannot stat " + path); }
+    size_ = (size_t)st.st_size;
+  }
+  FileReader(FileReader&& o) noexcept : size_(o.size_), fd_(o.fd_) { o.size_ = 0; o.fd_ = -1; }
+  FileReader& operator=(FileReader&& o) noexcept {
+    if (this != &o) { if (fd_ >= 0) ::close(fd_); size_ = o.size_; fd_ = o.fd_; o.size_ = 0; o.fd_ = -1; }
+    return *this;
+  }
+  FileReader(const FileReader&) = delete;
+  FileReader& operator=(const FileReader&) = delete;
+  ~FileReader() { if (fd_ >= 0) ::close(fd_); }
+  size_t size() const { return size_; }
+  void read_at(void* dst, size_t bytes, size_t offset) const {
+    uint8_t* d = (uint8_t*)dst;
+    while (bytes > 0) {
+      const ssize_t n = ::pread(fd_, d, bytes, (off_t)offset);
+      if (n <= 0) throw std::runtime_error("DICOM: short read");
+      d += n; offset += (size_t)n; bytes -= (size_t)n;
+    }
+  }
+  // header of the slice; reads 16 KiB first and the whole file only if the header is longer than that
+  View view() const {
+    std::vector<uint8_t> head(std::min<size_t>(size_, 16384));
+    read_at(head.data(), head.size(), 0);
+    try {
+      return parse_view(head.data(), head.size(), size_);
+    } catch (const NeedMore&) {
+      head.resize(size_);
+      read_at(head.data(), size_, 0);
+      return parse_view(head.data(), size_, size_);
+    }
+  }
+ private:
+  size_t size_ = 0;
+  int fd_ = -1;
+};
 
 inline std::vector<uint8_t> read_file(const std::string& path) {
   std::ifstream f(path, std::ios::binary);
