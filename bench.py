@@ -342,7 +342,7 @@ def main():
         # K1 in this configuration must read 2 B/px of int16 and write the 1-bit/px predicate plane
         k1_bytes = SLICES * W * H * (2.0 + 1.0 / 8.0)
         # DRAM traffic of one K1 launch from the latest committed `ncu --set full` capture of this command
-        traffic, traffic_src = None, None
+        traffic, traffic_src, alu = None, None, None
         try:
             import glob
             cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_summary.json")))
@@ -351,6 +351,10 @@ def main():
                 k1s = next(v for k, v in summ.items() if "k1_preprocess" in k)
                 traffic = k1s["dram_read_bytes"] + k1s["dram_write_bytes"]
                 traffic_src = "profiles/" + os.path.basename(cand[-1])
+                # the unit that actually binds K1: share of the ALU pipe's issue slots in that capture
+                alu = {"alu_pipe_pct_of_peak_active": float(k1s["alu_pipe_pct_active"]),
+                       "issue_slots_pct_active": float(k1s["issue_active_pct"]),
+                       "warp_instructions_per_launch": float(k1s["warp_inst"]), "source": traffic_src}
         except Exception:
             pass
         k1_avg_ms = k1_ms / max(calls, 1)
@@ -377,6 +381,7 @@ def main():
                          "share_of_step": (k1_ms / max(calls, 1)) / (ms / args.steps) if ms > 0 else None,
                          "sampled_launches": calls,
                          "k23_avg_launch_ms": k23_ms / max(calls, 1),
+                         "binding_unit": alu,
                          "note": "K1 is bound by the integer min/max pipe (7x7 median), not HBM; see DESIGN.md"},
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{reps} x one 24-slice 512x512 series ({cpu_dt:.1f} s), OpenMP batch-of-25"},
