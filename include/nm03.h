@@ -88,6 +88,9 @@ void nm03_shutdown(nm03_ctx* ctx);
 const char* nm03_last_error(void);
 int nm03_version(void);
 int nm03_gpu_count(const nm03_ctx* ctx);
+/* Number of CUDA devices visible to the process (0 if none); lets a driver build the gpu_ids list for
+ * nm03_init.  No counterpart in the reference, which uses whatever single device FAST picks. */
+int nm03_device_count(void);
 
 /* Literals of main_sequential.cpp:196,200,204,208,233,250 (erosion off, default switches). */
 void nm03_default_params(nm03_params* p);

@@ -19,7 +19,7 @@ EXPORTS = [
     "nm03_init", "nm03_shutdown", "nm03_last_error", "nm03_version", "nm03_gpu_count", "nm03_default_params",
     "nm03_make_seeds", "nm03_process_batch", "nm03_process_batch_device", "nm03_host_alloc", "nm03_host_free",
     "nm03_preprocess", "nm03_region_grow", "nm03_morphology", "nm03_kernel_launches",
-    "nm03_profile_enable", "nm03_profile_read", "nm03_process_batch_device_noalloc",
+    "nm03_profile_enable", "nm03_profile_read", "nm03_process_batch_device_noalloc", "nm03_device_count",
 ]
 
 NOALLOC_MAX_PRED_WORDS = 256 * 1024  # NM03_NOALLOC_MAX_PRED_WORDS

@@ -705,6 +705,11 @@ void nm03_shutdown(nm03_ctx* ctx) {
 
 int nm03_gpu_count(const nm03_ctx* ctx) { return ctx ? (int)ctx->workers.size() : 0; }
 
+int nm03_device_count(void) {
+  int count = 0;
+  return cudaGetDeviceCount(&count) == cudaSuccess ? count : 0;
+}
+
 long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu) {
   if (!ctx || gpu < 0 || gpu >= (int)ctx->workers.size()) return -1;
   return ctx->workers[gpu]->launches.load();

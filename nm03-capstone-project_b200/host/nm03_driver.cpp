@@ -267,7 +267,10 @@ int runBatch(const Options& opt) {
   if (patients.empty()) return 0;
   fs::create_directories(opt.out);
   nm03_ctx* ctx = nullptr;
-  if (nm03_init(opt.gpus.empty() ? nullptr : opt.gpus.data(), (int)opt.gpus.size(), &ctx) != NM03_OK) {
+  std::vector<int> gpus = opt.gpus;
+  if (gpus.empty() && opt.mode != "sequential")   // default: every visible GPU, patients sharded across them
+    for (int g = 0; g < nm03_device_count(); ++g) gpus.push_back(g);
+  if (nm03_init(gpus.empty() ? nullptr : gpus.data(), (int)gpus.size(), &ctx) != NM03_OK) {
     std::cerr << "Fatal error: " << nm03_last_error() << std::endl;
     return 1;
   }
