@@ -45,6 +45,30 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def bind_to_gpu_numa_node(torch, index):
+    """Restrict this rank (and the feeder threads it starts later) to the CPUs of the NUMA node its GPU hangs off, so the
+    pinned staging buffers are first-touched in the memory next to that GPU's PCIe root.  Returns a note for `config`."""
+    if os.environ.get("NM03_BENCH_NUMA", "1") == "0":
+        return "off"
+    try:
+        p = torch.cuda.get_device_properties(index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return "single node"
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return f"node {node} has no cpu in this process's mask"
+        os.sched_setaffinity(0, allowed)
+        return f"node {node}, {len(allowed)} cpus"
+    except (OSError, AttributeError, ValueError) as e:
+        return f"unavailable ({type(e).__name__})"
+
+
 def load_oracle():
     """CPU oracle — used ONLY for the cpu_baseline / --impl reference legs."""
     so = os.path.join(ROOT, "oracle", "libnm03_oracle.so")
@@ -240,6 +264,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    full_mask = os.sched_getaffinity(0)
+    numa_note = bind_to_gpu_numa_node(torch, local_rank) if world > 1 else "not needed at 1 GPU"
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -250,46 +276,66 @@ def main():
 
     # ---- resident inputs (larger than L2), outputs ------------------------------------------
     d_in = torch_series(torch, N_SERIES, dev, 1234 + rank)
-    d_out = torch.empty((2, SLICES, H, W), dtype=torch.uint8, device=dev)
+    # Device-resident steps are issued round-robin on a few streams (a resident caller with more than one series in
+    # flight): the library keeps a scratch slot per calling stream, so the latency-bound fill/morphology kernel of
+    # one series runs under the ALU-bound K1 of the next.  NM03_BENCH_STREAMS=1 gives the single-stream figure.
+    n_streams = max(1, min(4, int(os.environ.get("NM03_BENCH_STREAMS", "4"))))
+    streams = [torch.cuda.Stream(device=dev) for _ in range(n_streams)]
+    stream = streams[0]
+    d_out = torch.empty((max(2, n_streams), SLICES, H, W), dtype=torch.uint8, device=dev)   # one per stream in flight
     outs = []
-    for i in range(2):
+    for i in range(d_out.shape[0]):
         o = nm03.Outputs()
         o.dilated = d_out[i].data_ptr()
         outs.append(o)
-    stream = torch.cuda.Stream(device=dev)
 
-    PROFILE_EVERY = 8   # per-kernel CUDA events are recorded on every 8th step of the timed region only:
-                        # an event between the two kernels defeats their programmatic overlap (~6 % per step)
-
-    def step(i, timed=False):
-        if timed:
-            ctx.profile_enable(i % PROFILE_EVERY == 0)
-        ctx.process_batch_device(d_in[i % N_SERIES].data_ptr(), SLICES, W, H, params, outs[i & 1], stream.cuda_stream)
+    def step(i, n_str):
+        ctx.process_batch_device(d_in[i % N_SERIES].data_ptr(), SLICES, W, H, params, outs[i % len(outs)],
+                                 streams[i % n_str].cuda_stream)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    with torch.cuda.stream(stream):
-        for i in range(args.warmup):
-            step(i)
-        barrier()
-        assert int(d_out[(args.warmup - 1) & 1].sum().item()) > 0, "pipeline produced empty masks"
-        sampler = ClockSampler(local_rank)
-        sampler.start()
-        launches0 = ctx.kernel_launches()
+    def timed_region(steps, n_str):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
-        e0.record(stream)
-        for i in range(args.steps):
-            step(args.warmup + i, timed=True)
+        e0.record(stream)                      # every stream is idle here (barrier synchronised the device)
+        for i in range(steps):
+            step(args.warmup + i, n_str)
+        for other in streams[1:n_str]:
+            stream.wait_stream(other)          # e1 fires after the last step of every stream
         e1.record(stream)
         barrier()
-        ms = e0.elapsed_time(e1)
-        k1_ms, k23_ms, calls = ctx.profile_read()
-        ctx.profile_enable(False)
-        launches = ctx.kernel_launches() - launches0
+        return e0.elapsed_time(e1)
+
+    for i in range(args.warmup):
+        step(i, n_streams)
+    barrier()
+    assert int(d_out[(args.warmup - 1) % len(outs)].sum().item()) > 0, "pipeline produced empty masks"
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = ctx.kernel_launches()
+    ms = timed_region(args.steps, n_streams)
+    launches = ctx.kernel_launches() - launches0
+
+    # Per-kernel durations for the roofline: the same steps once more on ONE stream, where a kernel's CUDA-event
+    # duration is its own (with two streams the events of one step also span the neighbouring step's kernels).
+    # Events are recorded around each kernel on every 8th step only: an event between K1 and K23 defeats their
+    # programmatic overlap (~6 % per step).
+    PROFILE_EVERY = 8
+    serial_steps = min(args.steps, 1000)
+    real_step = step
+
+    def step(i, n_str):   # noqa: F811 - the profiled variant of the same call
+        ctx.profile_enable(i % PROFILE_EVERY == 0)
+        real_step(i, n_str)
+
+    serial_ms = timed_region(serial_steps, 1)
+    k1_ms, k23_ms, calls = ctx.profile_read()
+    ctx.profile_enable(False)
+    step = real_step
 
     # ---- e2e: pinned host buffers through the public entry point ------------------------------
     # Two feeder threads per GPU (the driver's structure, nm03_driver.cpp --streams 2) call the blocking
@@ -325,13 +371,13 @@ def main():
     assert all(int(h.sum()) > 0 for h in h_outs)
 
     # ---- max over ranks ------------------------------------------------------------------------
-    t = torch.tensor([ms, e2e_s * 1000.0, k1_ms, k23_ms], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, e2e_s * 1000.0, k1_ms, k23_ms, serial_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         tl = torch.tensor([float(launches)], dtype=torch.float64, device=dev)
         dist.all_reduce(tl, op=dist.ReduceOp.SUM)
         launches = int(tl.item())
-    ms, e2e_ms, k1_ms, k23_ms = [float(x) for x in t.tolist()]
+    ms, e2e_ms, k1_ms, k23_ms, serial_ms = [float(x) for x in t.tolist()]
 
     if rank == 0:
         try:
@@ -360,6 +406,7 @@ def main():
         k1_avg_ms = k1_ms / max(calls, 1)
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
         oracle = load_oracle()
+        os.sched_setaffinity(0, full_mask)
         threads = host_threads()
         cpu_val, reps, cpu_dt = time_cpu(oracle, h_in[0].copy(), threads, args.cpu_seconds, 1000)
         line = {
@@ -368,7 +415,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "s16x2 min/max + f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "slices_per_step_per_gpu": SLICES, "parallelism": f"patient-range x{world}",
                        "l2": f"rotating {N_SERIES} distinct resident series ({N_SERIES * SLICES * W * H * 2 >> 20} MiB > 126 MB L2)",
-                       "outputs": "dilated uint8 mask", "jpeg_export": "host stage; reported separately under pipeline_with_io"},
+                       "outputs": "dilated uint8 mask", "resident_streams": n_streams, "jpeg_export": "host stage; reported separately under pipeline_with_io",
+                       "rank_numa_binding": numa_note},
             "e2e": {"value": world * e2e_steps * SLICES / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": SLICES * W * H * 2, "d2h_bytes_per_step": SLICES * W * H,
                     "steps": e2e_steps, "api": f"nm03_process_batch (pinned host in/out), {n_feed} feeder threads per GPU"},
@@ -378,7 +426,11 @@ def main():
                          "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src,
                          "avg_launch_ms": k1_avg_ms, "bytes_per_launch": k1_bytes,
-                         "share_of_step": (k1_ms / max(calls, 1)) / (ms / args.steps) if ms > 0 else None,
+                         "measured_on": f"{serial_steps} steps of the same workload on one stream, events on every "
+                                        f"{PROFILE_EVERY}th step (the headline region runs {n_streams} streams, where "
+                                        "kernels of neighbouring steps overlap)",
+                         "single_stream_ms_per_step": serial_ms / serial_steps,
+                         "share_of_step": (k1_ms / max(calls, 1)) / (serial_ms / serial_steps) if serial_ms > 0 else None,
                          "sampled_launches": calls,
                          "k23_avg_launch_ms": k23_ms / max(calls, 1),
                          "binding_unit": alu,

@@ -54,6 +54,7 @@ struct Slot {
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;     // recorded after the last use of this slot's scratch
   bool used = false;
+  cudaStream_t last_stream = nullptr;  // the stream `done` was last recorded on
   uint32_t* pred = nullptr;       // scratch: predicate bit-plane [n][h][wpr]
   size_t pred_bytes = 0;
   void* stage_in = nullptr;       // scratch: device copy of host inputs
@@ -110,11 +111,20 @@ struct DeviceGuard {
   }
 };
 
-Slot* acquire(Worker* wk, bool block = true) {
+// `prefer` = the caller's own stream (device entry point): a free slot last used on that stream needs no
+// cross-stream wait, a never-used one neither, so callers that alternate between a few streams each settle
+// on a slot of their own and their batches overlap on the GPU.
+Slot* acquire(Worker* wk, bool block = true, cudaStream_t prefer = nullptr) {
   std::unique_lock<std::mutex> lk(wk->mu);
   for (;;) {
-    for (auto& s : wk->slots)
-      if (!s.busy) { s.busy = true; return &s; }
+    Slot* pick = nullptr;
+    for (auto& s : wk->slots) {
+      if (s.busy) continue;
+      if (!prefer) { pick = &s; break; }
+      if (s.used && s.last_stream == prefer) { pick = &s; break; }
+      if (!pick || (!s.used && pick->used)) pick = &s;
+    }
+    if (pick) { pick->busy = true; return pick; }
     if (!block) return nullptr;
     wk->cv.wait(lk);
   }
@@ -131,9 +141,22 @@ void release(Worker* wk, Slot* s) {
 struct SlotLease {
   Worker* wk;
   Slot* s;
-  explicit SlotLease(Worker* w) : wk(w), s(acquire(w)) {}
+  explicit SlotLease(Worker* w, cudaStream_t prefer = nullptr) : wk(w), s(acquire(w, true, prefer)) {}
   ~SlotLease() { release(wk, s); }
 };
+
+// Work queued earlier on another stream may still be using this slot's scratch.
+int order_after_last_use(Slot* s, cudaStream_t st) {
+  if (s->used && s->last_stream != st) CK(cudaStreamWaitEvent(st, s->done, 0));
+  return NM03_OK;
+}
+
+int mark_used(Slot* s, cudaStream_t st) {
+  CK(cudaEventRecord(s->done, st));
+  s->used = true;
+  s->last_stream = st;
+  return NM03_OK;
+}
 
 // grow-only scratch; growing waits for the slot's previous work first
 int ensure(Slot* s, void** buf, size_t* have, size_t need) {
@@ -469,7 +492,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   }
   const size_t pred_bytes = (size_t)n * h * pre.wpr * 4;
   if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pred_bytes))) return rc;
-  if (s->used && st != s->stream) CK(cudaStreamWaitEvent(st, s->done, 0));  // scratch reuse across streams
+  if ((rc = order_after_last_use(s, st))) return rc;
   if ((rc = ensure_lut(wk, s, st, pre))) return rc;
   if (!s->sched) {
     if ((rc = ensure(s, (void**)&s->sched, &s->sched_bytes, 2 * sizeof(unsigned int)))) return rc;
@@ -503,9 +526,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
     wk->prof_pending.push_back(rec);
   }
   wk->launches += 1;
-  CK(cudaEventRecord(s->done, st));
-  s->used = true;
-  return NM03_OK;
+  return mark_used(s, st);
 }
 
 }  // namespace
@@ -768,7 +789,7 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
   if (!d_slices || !d_out || n < 0) return fail(NM03_ERR_INVALID, "null buffer or negative count");
   if (n == 0) return NM03_OK;
   DeviceGuard g(wk->device);
-  SlotLease lease(wk);
+  SlotLease lease(wk, (cudaStream_t)stream);
   cudaStream_t st = stream ? (cudaStream_t)stream : lease.s->stream;
   return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out);
 }
@@ -873,6 +894,7 @@ int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, con
   DeviceGuard g(wk->device);
   SlotLease lease(wk);
   Slot* s = lease.s;
+  if ((rc = order_after_last_use(s, s->stream))) return rc;
   const size_t npx = (size_t)w * h, pw = (size_t)h * pre.wpr * 4;
   if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx * 2))) return rc;
   if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx * 8 + pw + 16))) return rc;
@@ -888,8 +910,7 @@ int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, con
   if (median) CK(cudaMemcpyAsync(median, pre.median, npx * 4, cudaMemcpyDeviceToHost, s->stream));
   if (sharpened) CK(cudaMemcpyAsync(sharpened, pre.sharpened, npx * 4, cudaMemcpyDeviceToHost, s->stream));
   if (predicate) CK(cudaMemcpyAsync(predicate, pre.predicate, pw, cudaMemcpyDeviceToHost, s->stream));
-  CK(cudaEventRecord(s->done, s->stream));
-  s->used = true;
+  if ((rc = mark_used(s, s->stream))) return rc;
   CK(cudaStreamSynchronize(s->stream));
   return NM03_OK;
 }
@@ -907,6 +928,7 @@ int nm03_region_grow(nm03_ctx* ctx, int gpu, const float* image, int w, int h, c
   DeviceGuard g(wk->device);
   SlotLease lease(wk);
   Slot* s = lease.s;
+  if ((rc = order_after_last_use(s, s->stream))) return rc;
   const size_t npx = (size_t)w * h, pw = (size_t)h * seg.wpr * 4;
   if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx * 4))) return rc;
   if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx + 16))) return rc;
@@ -921,8 +943,7 @@ int nm03_region_grow(nm03_ctx* ctx, int gpu, const float* image, int w, int h, c
   CK(cudaMemcpyAsync(mask, seg.rg_mask, npx, cudaMemcpyDeviceToHost, s->stream));
   int it = 0;
   CK(cudaMemcpyAsync(&it, seg.iterations, 4, cudaMemcpyDeviceToHost, s->stream));
-  CK(cudaEventRecord(s->done, s->stream));
-  s->used = true;
+  if ((rc = mark_used(s, s->stream))) return rc;
   CK(cudaStreamSynchronize(s->stream));
   if (iterations) *iterations = it;
   return NM03_OK;
@@ -946,6 +967,7 @@ int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, i
   DeviceGuard g(wk->device);
   SlotLease lease(wk);
   Slot* s = lease.s;
+  if ((rc = order_after_last_use(s, s->stream))) return rc;
   const size_t npx = (size_t)w * h, pw = (size_t)h * seg.wpr * 4;
   if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, npx))) return rc;
   if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, npx))) return rc;
@@ -958,8 +980,7 @@ int nm03_morphology(nm03_ctx* ctx, int gpu, const uint8_t* mask, int w, int h, i
   if ((rc = run_segment(wk, s, s->stream, seg))) return rc;
   wk->launches += 1;
   CK(cudaMemcpyAsync(out, s->stage_out, npx, cudaMemcpyDeviceToHost, s->stream));
-  CK(cudaEventRecord(s->done, s->stream));
-  s->used = true;
+  if ((rc = mark_used(s, s->stream))) return rc;
   CK(cudaStreamSynchronize(s->stream));
   return NM03_OK;
 }
