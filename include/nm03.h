@@ -110,7 +110,11 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
                        const int* seeds_xy, int n_seeds, const nm03_outputs* out, int* status);
 
 /* Same, but every buffer is already in the memory of GPU `gpu`; work is queued on `stream`
- * (a cudaStream_t passed as void*, NULL = the worker's own stream) and the call does not wait. */
+ * (a cudaStream_t passed as void*, NULL = the worker's own stream) and the call does not wait.
+ * The scratch between the two kernels belongs to one of 4 slots per GPU; a calling stream keeps the
+ * slot it used last, so a caller that rotates its batches over up to 4 streams gets them overlapped on
+ * the GPU (the fill kernel of one batch under the median kernel of the next); with more streams
+ * than slots a slot changes hands in stream order (event wait), never concurrently. */
 int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,
                               const nm03_params* params, const int* seeds_xy, int n_seeds,
                               const nm03_outputs* d_out, void* stream);
