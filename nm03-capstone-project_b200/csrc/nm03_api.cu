@@ -325,9 +325,19 @@ int fill_fast(nm03::PreParams& k, const nm03_params* p, int sharpen_half) {
     const double eb = u * (6.3 * gain + 2.1);
     // the truncated window is only worth it when it does not widen the band noticeably
     if (attempt == 0 && hs > 2 && ec > 4e-6) continue;
-    k.ea = (float)(ea * 1.02) + 1e-12f;
-    k.eb = (float)(eb * 1.02) + 1e-12f;
-    k.ec = (float)(ec * 1.02) + 1e-12f;
+    // The kernel classifies with d = fl(fl(|s - mid|) - half), mid/half the rounded centre and half-width of
+    // [rg_min, rg_max]; in exact arithmetic d = max(rg_min - s, s - rg_max).  Its rounding (two operations, two
+    // rounded constants) is below 4u(|s| + |rg_min| + |rg_max|) with |s| <= (1+|gain|)|v| + |gain||blur|, and
+    // is folded into the band, so outside the band the sign of d is the oracle's predicate.
+    const double rlo = p->rg_min, rhi = p->rg_max;
+    k.rg_mid = (float)(0.5 * rlo + 0.5 * rhi);
+    k.rg_half = (float)(0.5 * rhi - 0.5 * rlo);
+    if (!std::isfinite(k.rg_mid) || !std::isfinite(k.rg_half)) return nm03::K1_EXACT;
+    const double ea2 = ea + 4.2 * u * gain, eb2 = eb + 4.2 * u * (1.0 + gain);
+    const double ec2 = ec + 4.2 * u * (std::fabs(rlo) + std::fabs(rhi));
+    k.ea = (float)(ea2 * 1.02) + 1e-12f;
+    k.eb = (float)(eb2 * 1.02) + 1e-12f;
+    k.ec = (float)(ec2 * 1.02) + 1e-12f;
     best_mode = (he < hs) ? nm03::K1_FAST_HE2 : nm03::K1_FAST_FULL;
     break;
   }

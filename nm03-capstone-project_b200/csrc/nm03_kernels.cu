@@ -493,6 +493,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       const int band = it / (K1_TW / 4), xq = it - band * (K1_TW / 4);
       const int oyl0 = band * RB;
       const int ox = x0 + 4 * xq;
+      const uint32_t xmask = ox + 3 < w ? 15u : (ox < w ? (1u << (w - ox)) - 1u : 0u);   // pixels inside the image
       float hsum[RB + 2 * HE][4], cv[RB][4];
 #pragma unroll
       for (int ri = 0; ri < RB + 2 * HE; ++ri) {
@@ -515,19 +516,23 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         const int oy = y0 + oyl0 + r;
         uint32_t nib = 0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 3; j >= 0; --j) {   // pixel 3 first: each sign bit is shifted in below the previous ones
           float blur = 0.0f;
 #pragma unroll
           for (int t = 0; t < NT; ++t) blur = __fmaf_rn(p.gx[t + (K1_HS_MAX - HE)], hsum[r + t][j], blur);
           const float v = cv[r][j];
           float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
           const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
-          if (fabsf(sv - p.rg_min) <= eps || fabsf(sv - p.rg_max) <= eps) {
+          // signed distance to the interval: negative inside; decided by its sign unless it lies in the band
+          float d = __fsub_rn(fabsf(__fsub_rn(sv, p.rg_mid)), p.rg_half);
+          if (fabsf(d) <= eps) {
             const float be = blur1_exact<HS>(M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX, p);
             sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, be)));
+            d = (sv >= p.rg_min && sv <= p.rg_max) ? -1.0f : 1.0f;
           }
-          if (ox + j < w && sv >= p.rg_min && sv <= p.rg_max) nib |= 1u << j;
+          nib = __funnelshift_l(__float_as_uint(d), nib, 1);
         }
+        nib &= xmask;
         uint32_t word = nib << (4 * (lane & 7));
         word |= __shfl_xor_sync(0xffffffffu, word, 1);
         word |= __shfl_xor_sync(0xffffffffu, word, 2);
