@@ -5,6 +5,7 @@
 #include "dicom.hpp"
 #include "jpeg.hpp"
 #include "phantom.hpp"
+#include "nm03.hpp"
 
 extern "C" {
 
@@ -41,6 +42,35 @@ long nm03h_jpeg_encode(const uint8_t* px, int w, int h, int channels, int qualit
     std::memcpy(out, b.data(), b.size());
     return (long)b.size();
   } catch (const std::exception&) { return 0; }
+}
+
+// ImageRenderer on a 16-bit slice -> RGB canvas [ch][cw][3] over black (main_sequential.cpp:258-259)
+int nm03h_render_image(const void* px, int w, int h, int is_unsigned, int cw, int ch, uint8_t* rgb) {
+  try {
+    auto img = std::make_shared<nm03::Image>(w, h, is_unsigned ? nm03::TYPE_UINT16 : nm03::TYPE_INT16);
+    std::memcpy(img->data(), px, (size_t)w * h * 2);
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), cw, ch);
+    rti->connect(nm03::ImageRenderer::create()->addInputData(img));
+    rti->update();
+    std::memcpy(rgb, rti->getOutputData<nm03::Image>(0)->data(), (size_t)cw * ch * 3);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
+// SegmentationRenderer(label 1 = white, opacity, borderOpacity, borderRadius) over black (main_sequential.cpp:261)
+int nm03h_render_segmentation(const uint8_t* lab, int w, int h, int cw, int ch, float opacity, float border_opacity, int radius,
+                              uint8_t* rgb) {
+  try {
+    auto img = std::make_shared<nm03::Image>(w, h, nm03::TYPE_UINT8);
+    std::memcpy(img->data(), lab, (size_t)w * h);
+    nm03::LabelColors colors;
+    colors[1] = nm03::Color::White();
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), cw, ch);
+    rti->connect(nm03::SegmentationRenderer::create(colors, opacity, border_opacity, radius)->addInputData(img));
+    rti->update();
+    std::memcpy(rgb, rti->getOutputData<nm03::Image>(0)->data(), (size_t)cw * ch * 3);
+    return 0;
+  } catch (const std::exception&) { return -1; }
 }
 
 }  // extern "C"

@@ -7,8 +7,13 @@
 // quantisation tables are the example tables of T.81 Annex K; 4:4:4, no restart markers.
 #pragma once
 #include <cmath>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#include <xmmintrin.h>
+#endif
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -22,6 +27,7 @@ static const uint8_t kZigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18
                                     41, 34, 27, 20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22,
                                     15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55,
                                     62, 63};
+static const uint8_t kUnzigzag[64] = {0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42, 3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};  // natural index -> zigzag position
 static const uint8_t kQLuma[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57,
                                    69, 56, 14, 17, 22, 29, 51, 87, 80, 62, 18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55,
                                    64, 81, 104, 113, 92, 49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100,
@@ -70,54 +76,141 @@ struct Huff {
   }
 };
 
+// Entropy-coded segment writer: bits collect in a 64-bit accumulator and leave four bytes at a time;
+// a word without any 0xFF byte (nearly all of them) is stored whole, the others byte by byte with
+// the 0x00 stuffing byte of T.81 B.1.1.5.  The caller keeps at least 16 bytes of room at `p`.
 struct BitWriter {
-  std::vector<uint8_t>& out;
-  uint32_t acc = 0;
+  uint8_t* p;
+  uint64_t acc = 0;
   int nbits = 0;
-  explicit BitWriter(std::vector<uint8_t>& o) : out(o) {}
-  void put(uint32_t code, int len) {
-    acc = (acc << len) | (code & ((1u << len) - 1u));
+  explicit BitWriter(uint8_t* dst) : p(dst) {}
+  inline void put(uint32_t bits, int len) {  // bits < 2^len, len <= 27
+    acc = (acc << len) | bits;
     nbits += len;
-    while (nbits >= 8) {
-      const uint8_t b = (uint8_t)(acc >> (nbits - 8));
-      out.push_back(b);
-      if (b == 0xFF) out.push_back(0);  // byte stuffing
-      nbits -= 8;
+    if (nbits >= 32) {
+      const uint32_t w = (uint32_t)(acc >> (nbits - 32));
+      nbits -= 32;
+      if (((w & ~(w + 0x01010101u)) & 0x80808080u) == 0) {   // no byte of w is 0xFF
+        p[0] = (uint8_t)(w >> 24); p[1] = (uint8_t)(w >> 16); p[2] = (uint8_t)(w >> 8); p[3] = (uint8_t)w;
+        p += 4;
+      } else {
+        for (int sh = 24; sh >= 0; sh -= 8) {
+          const uint8_t b = (uint8_t)(w >> sh);
+          *p++ = b;
+          if (b == 0xFF) *p++ = 0;
+        }
+      }
     }
   }
-  void flush() { if (nbits > 0) put(0x7F, 8 - nbits); }
+  inline void flush() {  // pad the last byte with 1-bits
+    while (nbits >= 8) {
+      const uint8_t b = (uint8_t)(acc >> (nbits - 8));
+      *p++ = b;
+      if (b == 0xFF) *p++ = 0;
+      nbits -= 8;
+    }
+    if (nbits > 0) {
+      const uint8_t b = (uint8_t)(((acc << (8 - nbits)) | (0xFFu >> nbits)) & 0xFFu);
+      *p++ = b;
+      if (b == 0xFF) *p++ = 0;
+      nbits = 0;
+    }
+  }
 };
 
 // 8-point forward DCT after Arai, Agui and Nakajima: 5 multiplications and 29 additions per
 // transform; the outputs are scaled by kAan[u] (times 8 for the 2-D transform), which the caller folds
-// into its reciprocal quantisation table.
+// into its reciprocal quantisation table.  One template serves the scalar path (T = float) and the
+// SSE2 path (T = four transforms side by side); both perform the same operations in the same order,
+// so their results are identical.
 static const float kAan[8] = {1.0f, 1.387039845f, 1.306562965f, 1.175875602f, 1.0f, 0.785694958f, 0.541196100f, 0.275899379f};
 
-inline void aan8(float* d, int stride) {
-  const float t0 = d[0] + d[7 * stride], t7 = d[0] - d[7 * stride];
-  const float t1 = d[stride] + d[6 * stride], t6 = d[stride] - d[6 * stride];
-  const float t2 = d[2 * stride] + d[5 * stride], t5 = d[2 * stride] - d[5 * stride];
-  const float t3 = d[3 * stride] + d[4 * stride], t4 = d[3 * stride] - d[4 * stride];
-  const float e0 = t0 + t3, e3 = t0 - t3, e1 = t1 + t2, e2 = t1 - t2;
-  d[0] = e0 + e1;
-  d[4 * stride] = e0 - e1;
-  const float z1 = (e2 + e3) * 0.707106781f;
-  d[2 * stride] = e3 + z1;
-  d[6 * stride] = e3 - z1;
-  const float o0 = t4 + t5, o1 = t5 + t6, o2 = t6 + t7;
-  const float z5 = (o0 - o2) * 0.382683433f;
-  const float z2 = 0.541196100f * o0 + z5, z4 = 1.306562965f * o2 + z5, z3 = o1 * 0.707106781f;
-  const float z11 = t7 + z3, z13 = t7 - z3;
-  d[5 * stride] = z13 + z2;
-  d[3 * stride] = z13 - z2;
-  d[stride] = z11 + z4;
-  d[7 * stride] = z11 - z4;
+template <typename T, typename C>
+inline void aan8(T& d0, T& d1, T& d2, T& d3, T& d4, T& d5, T& d6, T& d7, C c) {
+  const T t0 = d0 + d7, t7 = d0 - d7, t1 = d1 + d6, t6 = d1 - d6;
+  const T t2 = d2 + d5, t5 = d2 - d5, t3 = d3 + d4, t4 = d3 - d4;
+  const T e0 = t0 + t3, e3 = t0 - t3, e1 = t1 + t2, e2 = t1 - t2;
+  d0 = e0 + e1;
+  d4 = e0 - e1;
+  const T z1 = (e2 + e3) * c(0.707106781f);
+  d2 = e3 + z1;
+  d6 = e3 - z1;
+  const T o0 = t4 + t5, o1 = t5 + t6, o2 = t6 + t7;
+  const T z5 = (o0 - o2) * c(0.382683433f);
+  const T z2 = c(0.541196100f) * o0 + z5, z4 = c(1.306562965f) * o2 + z5, z3 = o1 * c(0.707106781f);
+  const T z11 = t7 + z3, z13 = t7 - z3;
+  d5 = z13 + z2;
+  d3 = z13 - z2;
+  d1 = z11 + z4;
+  d7 = z11 - z4;
 }
 
-inline void fdct8x8_scaled(float* d) {
-  for (int y = 0; y < 8; ++y) aan8(d + 8 * y, 1);
-  for (int x = 0; x < 8; ++x) aan8(d + x, 8);
+inline void fdct8x8_scaled(float* d) {  // rows, then columns
+  auto c = [](float x) { return x; };
+  for (int y = 0; y < 8; ++y) { float* r = d + 8 * y; aan8(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], c); }
+  for (int x = 0; x < 8; ++x) { float* q = d + x; aan8(q[0], q[8], q[16], q[24], q[32], q[40], q[48], q[56], c); }
 }
+
+// level shift, forward DCT and quantisation of one block -> 64 integers in natural (row-major) order
+inline void quantise_scalar(float* blk, const float* rq, int* out) {
+  fdct8x8_scaled(blk);
+  for (int i = 0; i < 64; ++i) {
+    const float qv = blk[i] * rq[i];
+    out[i] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+  }
+}
+
+#if defined(__SSE2__)
+struct V4 {
+  __m128 v;
+  V4() = default;
+  V4(__m128 x) : v(x) {}
+  friend inline V4 operator+(V4 a, V4 b) { return _mm_add_ps(a.v, b.v); }
+  friend inline V4 operator-(V4 a, V4 b) { return _mm_sub_ps(a.v, b.v); }
+  friend inline V4 operator*(V4 a, V4 b) { return _mm_mul_ps(a.v, b.v); }
+};
+
+// Same block transform with four 1-D transforms per instruction.  src: 8 rows of 8 bytes (stride in
+// bytes).  The row pass runs on transposed 4x4 tiles (lane = row), the column pass on the tiles
+// transposed back (lane = column), so the result lands in natural order.
+inline void quantise_sse2(const uint8_t* src, size_t stride, const float* rq, int* out) {
+  auto c = [](float x) { return V4(_mm_set1_ps(x)); };
+  const __m128i zero = _mm_setzero_si128();
+  const __m128 bias = _mm_set1_ps(128.0f);
+  __m128 r[8][2];
+  for (int y = 0; y < 8; ++y) {
+    const __m128i b8 = _mm_loadl_epi64(reinterpret_cast<const __m128i*>(src + y * stride));
+    const __m128i w16 = _mm_unpacklo_epi8(b8, zero);
+    r[y][0] = _mm_sub_ps(_mm_cvtepi32_ps(_mm_unpacklo_epi16(w16, zero)), bias);
+    r[y][1] = _mm_sub_ps(_mm_cvtepi32_ps(_mm_unpackhi_epi16(w16, zero)), bias);
+  }
+  V4 col[2][8];  // col[g][x]: column x, lanes = rows 4g..4g+3
+  for (int g = 0; g < 2; ++g)
+    for (int xh = 0; xh < 2; ++xh) {
+      __m128 a = r[4 * g][xh], b = r[4 * g + 1][xh], cc = r[4 * g + 2][xh], d = r[4 * g + 3][xh];
+      _MM_TRANSPOSE4_PS(a, b, cc, d);
+      col[g][4 * xh] = a; col[g][4 * xh + 1] = b; col[g][4 * xh + 2] = cc; col[g][4 * xh + 3] = d;
+    }
+  for (int g = 0; g < 2; ++g)
+    aan8(col[g][0], col[g][1], col[g][2], col[g][3], col[g][4], col[g][5], col[g][6], col[g][7], c);
+  V4 row[2][8];  // row[uh][y]: row y, lanes = horizontal frequencies 4uh..4uh+3
+  for (int g = 0; g < 2; ++g)
+    for (int uh = 0; uh < 2; ++uh) {
+      __m128 a = col[g][4 * uh].v, b = col[g][4 * uh + 1].v, cc = col[g][4 * uh + 2].v, d = col[g][4 * uh + 3].v;
+      _MM_TRANSPOSE4_PS(a, b, cc, d);
+      row[uh][4 * g] = a; row[uh][4 * g + 1] = b; row[uh][4 * g + 2] = cc; row[uh][4 * g + 3] = d;
+    }
+  for (int uh = 0; uh < 2; ++uh)
+    aan8(row[uh][0], row[uh][1], row[uh][2], row[uh][3], row[uh][4], row[uh][5], row[uh][6], row[uh][7], c);
+  const __m128 half = _mm_set1_ps(0.5f), sign = _mm_castsi128_ps(_mm_set1_epi32((int)0x80000000u));
+  for (int v = 0; v < 8; ++v)
+    for (int uh = 0; uh < 2; ++uh) {
+      const __m128 qv = _mm_mul_ps(row[uh][v].v, _mm_loadu_ps(rq + 8 * v + 4 * uh));
+      const __m128 h = _mm_or_ps(half, _mm_and_ps(qv, sign));   // +-0.5 with the sign of qv: round half away from zero
+      _mm_storeu_si128(reinterpret_cast<__m128i*>(out + 8 * v + 4 * uh), _mm_cvttps_epi32(_mm_add_ps(qv, h)));
+    }
+}
+#endif
 
 inline void marker(std::vector<uint8_t>& o, uint8_t m, const std::vector<uint8_t>& payload) {
   o.push_back(0xFF); o.push_back(m);
@@ -184,66 +277,112 @@ inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height,
     p.push_back(0); p.push_back(63); p.push_back(0);
     marker(o, 0xDA, p);
   }
-  BitWriter bw(o);
+  // entropy-coded segment, written straight into the tail of `o` (grown by block row)
+  const size_t kWorstBlock = 512;         // 64 coefficients x 26 bits, every byte stuffed, rounded up
+  const int blocks_per_row = ((width + 7) / 8) * channels;
+  size_t pos = o.size();
   int pred[3] = {0, 0, 0};
-  float blk[64];
-  for (int by = 0; by < height; by += 8)
+  BitWriter bw(nullptr);
+  auto bitsize = [](int v) { const unsigned a = (unsigned)(v < 0 ? -v : v); return a ? 32 - __builtin_clz(a) : 0; };
+  for (int by = 0; by < height; by += 8) {
+    if (o.size() - pos < (size_t)blocks_per_row * kWorstBlock + 64) o.resize(pos + (size_t)blocks_per_row * kWorstBlock * 2 + 64);
+    bw.p = o.data() + pos;
     for (int bx = 0; bx < width; bx += 8)
       for (int c = 0; c < channels; ++c) {
-        if (channels == 1 && by + 8 <= height && bx + 8 <= width) {
-          for (int y = 0; y < 8; ++y) {
-            const uint8_t* px = pixels + (size_t)(by + y) * width + bx;
-            for (int x = 0; x < 8; ++x) blk[y * 8 + x] = (float)px[x] - 128.0f;
-          }
-        } else
-        for (int y = 0; y < 8; ++y)
-          for (int x = 0; x < 8; ++x) {
-            const int sy = by + y < height ? by + y : height - 1, sx = bx + x < width ? bx + x : width - 1;
-            const uint8_t* px = pixels + ((size_t)sy * width + sx) * channels;
-            float v;
-            if (channels == 1) v = px[0];
-            else {
-              const float r = px[0], g = px[1], b = px[2];
-              v = c == 0 ? 0.299f * r + 0.587f * g + 0.114f * b
-                         : c == 1 ? -0.168736f * r - 0.331264f * g + 0.5f * b + 128.0f
-                                  : 0.5f * r - 0.418688f * g - 0.081312f * b + 128.0f;
-            }
-            blk[y * 8 + x] = v - 128.0f;
-          }
         const int t = c ? 1 : 0;
-        int zz[64];
-        bool flat = true;  // constant block (most of a rendered mask): only the DC term survives
-        for (int i = 1; i < 64 && flat; ++i) flat = blk[i] == blk[0];
-        if (flat) {
-          const float qv = blk[0] * 64.0f * rq[t][0];   // the scaled transform's DC output is the plain sum
-          zz[0] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
-          for (int i = 1; i < 64; ++i) zz[i] = 0;
+        int q[64];                        // quantised coefficients, natural order
+        bool dc_only = false;
+        if (channels == 1 && by + 8 <= height && bx + 8 <= width) {
+          const uint8_t* px = pixels + (size_t)by * width + bx;
+          // constant block (most of a rendered mask): only the DC term survives
+          uint64_t first, rowv;
+          std::memcpy(&first, px, 8);
+          bool flat = first == (first & 0xFFu) * 0x0101010101010101ull;
+          for (int y = 1; y < 8 && flat; ++y) { std::memcpy(&rowv, px + (size_t)y * width, 8); flat = rowv == first; }
+          if (flat) {
+            const float qv = ((float)px[0] - 128.0f) * 64.0f * rq[t][0];   // the scaled transform's DC output is the plain sum
+            q[0] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+            dc_only = true;
+          } else {
+#if defined(__SSE2__)
+            quantise_sse2(px, (size_t)width, rq[t], q);
+#else
+            float blk[64];
+            for (int y = 0; y < 8; ++y) for (int x = 0; x < 8; ++x) blk[y * 8 + x] = (float)px[(size_t)y * width + x] - 128.0f;
+            quantise_scalar(blk, rq[t], q);
+#endif
+          }
         } else {
-          fdct8x8_scaled(blk);
-          for (int i = 0; i < 64; ++i) {
-            const float qv = blk[kZigzag[i]] * rq[t][kZigzag[i]];
-            zz[i] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+          float blk[64];
+          for (int y = 0; y < 8; ++y)
+            for (int x = 0; x < 8; ++x) {
+              const int sy = by + y < height ? by + y : height - 1, sx = bx + x < width ? bx + x : width - 1;
+              const uint8_t* px = pixels + ((size_t)sy * width + sx) * channels;
+              float v;
+              if (channels == 1) v = px[0];
+              else {
+                const float r = px[0], g = px[1], b = px[2];
+                v = c == 0 ? 0.299f * r + 0.587f * g + 0.114f * b
+                           : c == 1 ? -0.168736f * r - 0.331264f * g + 0.5f * b + 128.0f
+                                    : 0.5f * r - 0.418688f * g - 0.081312f * b + 128.0f;
+              }
+              blk[y * 8 + x] = v - 128.0f;
+            }
+          bool flat = true;
+          for (int i = 1; i < 64 && flat; ++i) flat = blk[i] == blk[0];
+          if (flat) {
+            const float qv = blk[0] * 64.0f * rq[t][0];
+            q[0] = (int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+            dc_only = true;
+          } else {
+            quantise_scalar(blk, rq[t], q);
           }
         }
-        auto emit = [&](const Huff& h, int run_size, int value, int size) {
-          bw.put(h.code[run_size], h.len[run_size]);
-          if (size) bw.put((uint32_t)(value < 0 ? value - 1 : value), size);
-        };
-        auto bitsize = [](int v) { int a = v < 0 ? -v : v, s = 0; while (a) { ++s; a >>= 1; } return s; };
-        const int diff = zz[0] - pred[c];
-        pred[c] = zz[0];
-        emit(hdc[t], bitsize(diff), diff, bitsize(diff));
-        int run = 0;
-        for (int i = 1; i < 64; ++i) {
-          if (zz[i] == 0) { ++run; continue; }
-          while (run > 15) { bw.put(hac[t].code[0xF0], hac[t].len[0xF0]); run -= 16; }
-          const int s = bitsize(zz[i]);
-          emit(hac[t], (run << 4) | s, zz[i], s);
-          run = 0;
+        // DC difference, then (run, size) symbols of the AC terms in zigzag order; code and value bits go out together
+        const int diff = q[0] - pred[c];
+        pred[c] = q[0];
+        {
+          const int sz = bitsize(diff);
+          const uint32_t vb = (uint32_t)(diff < 0 ? diff - 1 : diff) & ((1u << sz) - 1u);
+          bw.put(((uint32_t)hdc[t].code[sz] << sz) | vb, hdc[t].len[sz] + sz);
         }
-        if (run) bw.put(hac[t].code[0x00], hac[t].len[0x00]);  // EOB
+        if (dc_only) { bw.put(hac[t].code[0x00], hac[t].len[0x00]); continue; }
+        // AC terms in zigzag order; a 64-bit map of the non-zero ones lets the loop jump from one to the next
+        alignas(16) int16_t zz[64];
+        for (int i = 0; i < 64; ++i) zz[kUnzigzag[i]] = (int16_t)q[i];
+        uint64_t nz = 0;
+#if defined(__SSE2__)
+        for (int k = 0; k < 4; ++k) {
+          const __m128i a = _mm_load_si128(reinterpret_cast<const __m128i*>(zz + 16 * k));
+          const __m128i b = _mm_load_si128(reinterpret_cast<const __m128i*>(zz + 16 * k + 8));
+          const int zero16 = _mm_movemask_epi8(_mm_cmpeq_epi8(_mm_packs_epi16(a, b), _mm_setzero_si128()));
+          nz |= (uint64_t)(uint16_t)~zero16 << (16 * k);
+        }
+#else
+        for (int i = 0; i < 64; ++i) nz |= (uint64_t)(zz[i] != 0) << i;
+#endif
+        nz &= ~(uint64_t)1;
+        int prev = 0;
+        while (nz) {
+          const int i = __builtin_ctzll(nz);
+          nz &= nz - 1;
+          int run = i - prev - 1;
+          prev = i;
+          while (run > 15) { bw.put(hac[t].code[0xF0], hac[t].len[0xF0]); run -= 16; }
+          const int v = zz[i];
+          const int sz = bitsize(v), rs = (run << 4) | sz;
+          const uint32_t vb = (uint32_t)(v < 0 ? v - 1 : v) & ((1u << sz) - 1u);
+          bw.put(((uint32_t)hac[t].code[rs] << sz) | vb, hac[t].len[rs] + sz);
+        }
+        if (prev != 63) bw.put(hac[t].code[0x00], hac[t].len[0x00]);  // EOB
       }
+    pos = (size_t)(bw.p - o.data());
+  }
+  if (o.size() - pos < 32) o.resize(pos + 32);
+  bw.p = o.data() + pos;
   bw.flush();
+  pos = (size_t)(bw.p - o.data());
+  o.resize(pos);
   o.push_back(0xFF); o.push_back(0xD9);  // EOI
   return o;
 }

@@ -19,6 +19,9 @@
 // label overlay, aspect-fit into the canvas).  Pixel parity with FAST's renderer is not claimed.
 #pragma once
 #include <nm03.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include <algorithm>
 #include <atomic>
@@ -99,6 +102,7 @@ class Image {
   template <class T> T* as() { return reinterpret_cast<T*>(bytes_.data()); }
   template <class T> const T* as() const { return reinterpret_cast<const T*>(bytes_.data()); }
   static size_t elemSize(DataType t) { return t == TYPE_FLOAT ? 4 : (t == TYPE_UINT8 || t == TYPE_INT8) ? 1 : 2; }
+  bool grey3 = false;   // hint set by RenderToImage: a 3-channel canvas whose channels are known to be equal
  private:
   int w_, h_, c_;
   DataType type_;
@@ -438,6 +442,7 @@ class Renderer : public ProcessObject {
  public:
   // paint this renderer's input into an RGB canvas (aspect-fit, centred)
   virtual void paint(uint8_t* rgb, int cw, int ch) = 0;
+  virtual bool paintsGrey() const { return false; }   // true: only ever writes r == g == b
  protected:
   Renderer() : ProcessObject(RENDERER) {}
   struct Fit { float scale; float ox, oy; };
@@ -452,10 +457,59 @@ class ImageRenderer : public Renderer {
   static std::shared_ptr<ImageRenderer> create() { return std::shared_ptr<ImageRenderer>(new ImageRenderer()); }
   std::shared_ptr<ImageRenderer> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return me(); }
   std::shared_ptr<ImageRenderer> addInputData(std::shared_ptr<Image> d) { connectData(std::move(d)); return me(); }
+  bool paintsGrey() const override { return true; }
   void paint(uint8_t* rgb, int cw, int ch) override {
     auto img = inputImage();
     const int w = img->getWidth(), h = img->getHeight();
     const size_t n = (size_t)w * h;
+    if (w == cw && h == ch && (img->getDataType() == TYPE_INT16 || img->getDataType() == TYPE_UINT16)) {
+      // the driver's case (16-bit slice on a canvas of its own size): same window and rounding as below, but the grey
+      // level of every intensity between min and max is tabulated once instead of being computed per pixel
+      const bool sg = img->getDataType() == TYPE_INT16;
+      const int16_t* ss = img->as<int16_t>();
+      const uint16_t* su = img->as<uint16_t>();
+      int lo_i = sg ? ss[0] : su[0], hi_i = lo_i;
+      size_t i0 = 0;
+#if defined(__SSE2__)
+      if (n >= 8) {   // signed 16-bit min/max, eight at a time (unsigned samples are biased into signed order)
+        const __m128i flip = _mm_set1_epi16(sg ? 0 : (short)0x8000);
+        __m128i mn = _mm_xor_si128(_mm_loadu_si128(reinterpret_cast<const __m128i*>(ss)), flip), mx = mn;
+        for (i0 = 8; i0 + 8 <= n; i0 += 8) {
+          const __m128i v = _mm_xor_si128(_mm_loadu_si128(reinterpret_cast<const __m128i*>(ss + i0)), flip);
+          mn = _mm_min_epi16(mn, v);
+          mx = _mm_max_epi16(mx, v);
+        }
+        alignas(16) int16_t a[8], b[8];
+        _mm_store_si128(reinterpret_cast<__m128i*>(a), mn);
+        _mm_store_si128(reinterpret_cast<__m128i*>(b), mx);
+        int lo_s = a[0], hi_s = b[0];
+        for (int k = 1; k < 8; ++k) { lo_s = std::min<int>(lo_s, a[k]); hi_s = std::max<int>(hi_s, b[k]); }
+        lo_i = sg ? lo_s : lo_s + 32768;
+        hi_i = sg ? hi_s : hi_s + 32768;
+      }
+#endif
+      if (sg) for (size_t i = i0; i < n; ++i) { lo_i = std::min<int>(lo_i, ss[i]); hi_i = std::max<int>(hi_i, ss[i]); }
+      else for (size_t i = i0; i < n; ++i) { lo_i = std::min<int>(lo_i, su[i]); hi_i = std::max<int>(hi_i, su[i]); }
+      const float lo = (float)lo_i, hi = (float)hi_i;
+      const float inv = hi > lo ? 255.0f / (hi - lo) : 0.0f;
+      std::vector<uint8_t> lut((size_t)(hi_i - lo_i) + 1);
+      for (size_t k = 0; k < lut.size(); ++k) {
+        const float g = ((float)(lo_i + (int)k) - lo) * inv;
+        lut[k] = (uint8_t)(int)(std::min(255.0f, std::max(0.0f, g)) + 0.5f);
+      }
+      size_t i = 0;
+      for (; i + 4 <= n; i += 4) {   // four pixels = twelve canvas bytes, written as three words
+        uint32_t g[4];
+        for (int k = 0; k < 4; ++k) g[k] = lut[(sg ? (int)ss[i + k] : (int)su[i + k]) - lo_i];
+        const uint32_t w0 = g[0] * 0x010101u | g[1] << 24, w1 = g[1] * 0x0101u | g[2] * 0x01010000u, w2 = g[2] | g[3] * 0x01010100u;
+        std::memcpy(rgb + 3 * i, &w0, 4); std::memcpy(rgb + 3 * i + 4, &w1, 4); std::memcpy(rgb + 3 * i + 8, &w2, 4);
+      }
+      for (; i < n; ++i) {
+        const uint8_t g = lut[(sg ? (int)ss[i] : (int)su[i]) - lo_i];
+        rgb[3 * i] = rgb[3 * i + 1] = rgb[3 * i + 2] = g;
+      }
+      return;
+    }
     std::vector<float> v(n);  // one conversion pass, then plain float indexing
     switch (img->getDataType()) {
       case TYPE_FLOAT: std::memcpy(v.data(), img->as<float>(), n * 4); break;
@@ -510,29 +564,68 @@ class SegmentationRenderer : public Renderer {
     const int w = img->getWidth(), h = img->getHeight();
     const uint8_t* lab = img->as<uint8_t>();
     const Fit f = fit(w, h, cw, ch);
-    auto label_at = [&](int x, int y) -> int { return (x < 0 || y < 0 || x >= w || y >= h) ? 0 : lab[(size_t)y * w + x]; };
+    const Color* table[256] = {};
+    for (auto& kv : colors_) if (kv.first >= 0 && kv.first < 256) table[kv.first] = &kv.second;
+    // A pixel is a border pixel when some pixel within borderRadius (disc, outside the image = label 0) carries
+    // another label.  Per labelled pixel, runr = how far its label extends unbroken to both sides in its row
+    // (capped at the radius); the disc test is then one comparison per row of the disc.
+    const int R = std::max(0, std::min(radius_, 127));
+    std::vector<int> hw(2 * R + 1);
+    for (int b = -R; b <= R; ++b) { int a = 0; while ((a + 1) * (a + 1) + b * b <= R * R) ++a; hw[b + R] = a; }
+    std::vector<uint8_t> runr((size_t)w * h, 0);
+    for (int y = 0; y < h; ++y) {
+      const uint8_t* row = lab + (size_t)y * w;
+      uint8_t* rr = runr.data() + (size_t)y * w;
+      for (int x = 0; x < w; ++x) {
+        if ((x & 7) == 0 && x + 8 <= w) {   // eight label-free pixels at once
+          uint64_t eight;
+          std::memcpy(&eight, row + x, 8);
+          if (eight == 0) { x += 7; continue; }
+        }
+        const int l = row[x];
+        if (l == 0) continue;
+        int k = 0;
+        while (k < R && x - k - 1 >= 0 && x + k + 1 < w && row[x - k - 1] == l && row[x + k + 1] == l) ++k;
+        rr[x] = (uint8_t)k;
+      }
+    }
+    auto is_border = [&](int x, int y, int l) {
+      for (int b = -R; b <= R; ++b) {
+        const int yy = y + b;
+        if (yy < 0 || yy >= h) return true;
+        const size_t i = (size_t)yy * w + x;
+        if (lab[i] != l || runr[i] < hw[b + R]) return true;
+      }
+      return false;
+    };
     std::vector<int> xs(cw);
     for (int cx = 0; cx < cw; ++cx) xs[cx] = (int)std::floor((cx + 0.5f - f.ox) / f.scale);
     for (int cy = 0; cy < ch; ++cy) {
       const int y = (int)std::floor((cy + 0.5f - f.oy) / f.scale);
       if (y < 0 || y >= h) continue;
       const uint8_t* row = lab + (size_t)y * w;
+      const bool identity = cw == w && ch == h;   // canvas pixel = image pixel
       for (int cx = 0; cx < cw; ++cx) {
+        if (identity && (cx & 7) == 0 && cx + 8 <= w) {
+          uint64_t eight;
+          std::memcpy(&eight, row + cx, 8);
+          if (eight == 0) { cx += 7; continue; }
+        }
         const int x = xs[cx];
         if (x < 0 || x >= w || row[x] == 0) continue;
         const int l = row[x];
-        auto it = colors_.find(l);
-        if (it == colors_.end()) continue;
-        bool border = false;  // within borderRadius of a pixel with another label
-        for (int b = -radius_; b <= radius_ && !border; ++b)
-          for (int a = -radius_; a <= radius_ && !border; ++a)
-            if (a * a + b * b <= radius_ * radius_ && label_at(x + a, y + b) != l) border = true;
-        const float op = border ? borderOpacity_ : opacity_;
+        const Color* col = table[l];
+        if (!col) continue;
+        const float op = is_border(x, y, l) ? borderOpacity_ : opacity_;
         uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
-        const float c[3] = {it->second.r, it->second.g, it->second.b};
+        const float c[3] = {col->r, col->g, col->b};
         for (int k = 0; k < 3; ++k) px[k] = (uint8_t)(int)(px[k] * (1 - op) + 255.0f * c[k] * op + 0.5f);
       }
     }
+  }
+  bool paintsGrey() const override {
+    for (auto& kv : colors_) if (kv.second.r != kv.second.g || kv.second.g != kv.second.b) return false;
+    return true;
   }
  private:
   SegmentationRenderer(LabelColors c, float o, float bo, int r) : colors_(std::move(c)), opacity_(o), borderOpacity_(bo), radius_(r) {}
@@ -557,7 +650,9 @@ class RenderToImage : public ProcessObject {
     const uint8_t bg[3] = {(uint8_t)std::lround(bg_.r * 255), (uint8_t)std::lround(bg_.g * 255), (uint8_t)std::lround(bg_.b * 255)};
     if (bg[0] == bg[1] && bg[1] == bg[2]) std::memset(rgb, bg[0], (size_t)w_ * h_ * 3);
     else for (size_t i = 0; i < (size_t)w_ * h_; ++i) { rgb[3 * i] = bg[0]; rgb[3 * i + 1] = bg[1]; rgb[3 * i + 2] = bg[2]; }
-    for (auto& r : renderers_) r->paint(rgb, w_, h_);
+    bool grey = bg[0] == bg[1] && bg[1] == bg[2];
+    for (auto& r : renderers_) { r->paint(rgb, w_, h_); grey = grey && r->paintsGrey(); }
+    img->grey3 = grey;
     output_ = img;
   }
  private:
@@ -579,10 +674,17 @@ class ImageFileExporter : public Typed<ImageFileExporter> {
         const uint8_t* p = img->as<uint8_t>();
         const size_t n = (size_t)img->getWidth() * img->getHeight();
         bool grey = true;
-        for (size_t i = 0; i < n && grey; ++i) grey = p[3 * i] == p[3 * i + 1] && p[3 * i] == p[3 * i + 2];
+        if (!img->grey3) for (size_t i = 0; i < n && grey; ++i) grey = p[3 * i] == p[3 * i + 1] && p[3 * i] == p[3 * i + 2];
         if (grey) {
           std::vector<uint8_t> g(n);
-          for (size_t i = 0; i < n; ++i) g[i] = p[3 * i];
+          size_t i = 0;
+          for (; i + 4 <= n; i += 4) {   // first channel of four pixels out of twelve bytes
+            uint32_t a, b, c;
+            std::memcpy(&a, p + 3 * i, 4); std::memcpy(&b, p + 3 * i + 4, 4); std::memcpy(&c, p + 3 * i + 8, 4);
+            const uint32_t o = (a & 0xFFu) | ((a >> 24) << 8) | (((b >> 16) & 0xFFu) << 16) | (((c >> 8) & 0xFFu) << 24);
+            std::memcpy(g.data() + i, &o, 4);
+          }
+          for (; i < n; ++i) g[i] = p[3 * i];
           jpeg::save(file_, g.data(), img->getWidth(), img->getHeight(), 1);
           return;
         }

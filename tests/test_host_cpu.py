@@ -113,3 +113,119 @@ def test_cpp_phantom_is_deterministic_and_in_spec(host):
     assert rc == 0 and 0 < r["dilated"].sum() < 0.3 * a.size     # blobs are segmented, not the whole head
     host.nm03h_phantom(512, 512, 3, 7, 1, b.ctypes.data_as(C.c_void_p))
     assert cm.o_pipeline(b)[1]["dilated"].mean() > 0.5           # low-contrast phantom covers > 50 %
+
+
+# ---- JPEG writer: byte-for-byte regression vectors ---------------------------------------------------
+def _jpeg_cases():
+    """Inputs of tests/golden/jpeg_md5.json (hashes of the encoder's output before its bit writer, DCT and
+    entropy loop were vectorised; the faster encoder must still produce the same bytes)."""
+    rng = np.random.default_rng(7)
+    yy, xx = np.mgrid[0:96, 0:128]
+    smooth = (127 + 100 * np.sin(xx / 9.0) * np.cos(yy / 7.0)).astype(np.uint8)
+    yield "smooth_q90", smooth, 90
+    yield "smooth_q35", smooth, 35
+    yield "noise_q90", rng.integers(0, 256, (64, 72)), 90
+    yield "noise_q100", rng.integers(0, 256, (40, 40)), 100
+    yield "extremes", np.where(rng.random((64, 64)) < 0.5, 0, 255), 95     # long codes, 0xFF bytes in the stream
+    yield "odd_size", (xx[:37, :51] * 5 + yy[:37, :51] * 3) % 256, 90
+    yield "flat", np.full((48, 48), 200), 90
+    mask = np.zeros((128, 128), np.uint8)
+    mask[30:90, 40:100] = 153
+    mask[50:60, 50:60] = 255
+    yield "mask", mask, 90
+    rgb = np.stack([smooth, np.roll(smooth, 5, 1), 255 - smooth], -1)
+    yield "rgb_q90", rgb, 90
+    yield "rgb_odd", rgb[:45, :77], 60
+    yield "big_noise", rng.normal(128, 40, (512, 512)).clip(0, 255), 90
+
+
+def _encode(host, img, quality):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape[:2]
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    out = np.empty(w * h * ch * 2 + 4096, np.uint8)
+    n = host.nm03h_jpeg_encode(img.ctypes.data_as(C.c_void_p), w, h, ch, quality, out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+    assert n > 0
+    return out[:n].tobytes()
+
+
+def test_jpeg_bytes_match_pinned_hashes(host):
+    import hashlib
+    import json
+    pinned = json.load(open(os.path.join(cm.ROOT, "tests", "golden", "jpeg_md5.json")))
+    seen = set()
+    for name, img, q in _jpeg_cases():
+        assert hashlib.md5(_encode(host, img, q)).hexdigest() == pinned[name], name
+        seen.add(name)
+    assert seen == set(pinned)
+
+
+def test_jpeg_stream_with_stuffed_bytes_decodes(host):
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    img = np.where(rng.random((72, 88)) < 0.5, 0, 255).astype(np.uint8)
+    data = _encode(host, img, 95)
+    assert b"\xff\x00" in data[600:]                      # the entropy-coded segment needed byte stuffing
+    dec = np.asarray(Image.open(io.BytesIO(data)))
+    assert dec.shape == img.shape and np.abs(dec.astype(int) - img).mean() < 12
+
+
+# ---- renderers (CPU restatement of FAST's GL renderers) against numpy/scipy --------------------------
+@pytest.mark.parametrize("unsigned", [0, 1])
+def test_image_renderer_identity_canvas(host, unsigned):
+    rng = np.random.default_rng(11)
+    if unsigned:
+        img = rng.integers(30000, 42000, (64, 80)).astype(np.uint16)     # crosses 32768
+    else:
+        img = rng.integers(-900, 3000, (64, 80)).astype(np.int16)
+    rgb = np.zeros((64, 80, 3), np.uint8)
+    assert host.nm03h_render_image(img.ctypes.data_as(C.c_void_p), 80, 64, unsigned, 80, 64, rgb.ctypes.data_as(C.c_void_p)) == 0
+    v = img.astype(np.float32)
+    lo, hi = v.min(), v.max()
+    g = (v - lo) * (np.float32(255.0) / (hi - lo))
+    exp = (np.minimum(np.float32(255), np.maximum(np.float32(0), g)) + np.float32(0.5)).astype(np.uint8)
+    for c in range(3):
+        np.testing.assert_array_equal(rgb[:, :, c], exp)
+
+
+def test_image_renderer_fits_a_smaller_slice_into_the_canvas(host):
+    img = (np.arange(32 * 48).reshape(32, 48) % 1000).astype(np.int16)
+    rgb = np.full((96, 96, 3), 7, np.uint8)
+    assert host.nm03h_render_image(img.ctypes.data_as(C.c_void_p), 48, 32, 0, 96, 96, rgb.ctypes.data_as(C.c_void_p)) == 0
+    assert (rgb[:15] == 0).all() and (rgb[-15:] == 0).all()      # 48x32 scaled by 2 -> 96x64, centred: black bars
+    assert rgb[16:80].max() >= 240 and (rgb[..., 0] == rgb[..., 1]).all()
+
+
+@pytest.mark.parametrize("radius", [0, 1, 2, 3])
+@pytest.mark.parametrize("canvas", [(90, 70), (180, 140), (128, 128)])
+def test_segmentation_renderer_border_rule(host, radius, canvas):
+    import scipy.ndimage as ndi
+    rng = np.random.default_rng(radius * 10 + canvas[0])
+    w, h = 90, 70
+    lab = (ndi.gaussian_filter(rng.random((h, w)), 2.5) > 0.5).astype(np.uint8)
+    lab[0:6, 10:30] = 1                                           # touches the image edge: outside counts as label 0
+    lab[40, 50] = 1
+    cw, ch = canvas
+    rgb = np.zeros((ch, cw, 3), np.uint8)
+    assert host.nm03h_render_segmentation(lab.ctypes.data_as(C.c_void_p), w, h, cw, ch, C.c_float(0.6), C.c_float(1.0), radius,
+                                          rgb.ctypes.data_as(C.c_void_p)) == 0
+    yy, xx = np.mgrid[-radius:radius + 1, -radius:radius + 1]
+    disc = (xx * xx + yy * yy) <= radius * radius
+    interior = ndi.binary_erosion(lab == 1, structure=disc, border_value=0) if radius > 0 else (lab == 1)
+    src = np.zeros((h, w), np.uint8)
+    src[lab == 1] = int(np.float32(255.0) * np.float32(1.0) * np.float32(1.0) + np.float32(0.5))         # border: opacity 1
+    src[interior] = int(np.float32(0) * np.float32(1 - np.float32(0.6)) + np.float32(255.0) * np.float32(0.6) + np.float32(0.5))
+    # aspect-fit, centred, nearest source pixel (the shim's mapping)
+    s = min(cw / w, ch / h)
+    ox, oy = (cw - w * s) * 0.5, (ch - h * s) * 0.5
+    exp = np.zeros((ch, cw), np.uint8)
+    for cy in range(ch):
+        y = int(np.floor((np.float32(cy) + np.float32(0.5) - np.float32(oy)) / np.float32(s)))
+        if not 0 <= y < h:
+            continue
+        for cx in range(cw):
+            x = int(np.floor((np.float32(cx) + np.float32(0.5) - np.float32(ox)) / np.float32(s)))
+            if 0 <= x < w:
+                exp[cy, cx] = src[y, x]
+    for c in range(3):
+        np.testing.assert_array_equal(rgb[:, :, c], exp)
