@@ -40,7 +40,7 @@ namespace {
 struct Options {
   std::string mode = "parallel", data, out = "../out-parallel", test_file, make_dataset;
   std::vector<int> gpus;
-  int batch = 25, streams = 3, host_threads = 0;   // 3 feeders per GPU measured best (25 900 slices/s from files in /dev/shm)
+  int batch = 25, streams = 3, host_threads = 0;   // 3 feeders per GPU measured best (21-29k slices/s from files in /dev/shm)
   bool do_export = true, dump_masks = false, lowcontrast = false;
   int patients = 20, slices = 24, size = 512;
 };
@@ -177,16 +177,28 @@ void exportSlice(const fs::path& dir, const std::string& file, const int16_t* ra
 
 struct Totals {
   std::atomic<long> ok{0}, total{0}, patients_ok{0};
+  std::atomic<long> ns_list{0}, ns_parse{0}, ns_read{0}, ns_gpu{0}, ns_export{0};  // feeder wall time per phase (NM03_DRIVER_TIMING=1 prints it)
   std::mutex log;
+};
+
+struct PhaseTimer {   // adds the time since construction (or the last lap) to a counter
+  Clock::time_point t = Clock::now();
+  void lap(std::atomic<long>& acc) {
+    const auto n = Clock::now();
+    acc += std::chrono::duration_cast<std::chrono::nanoseconds>(n - t).count();
+    t = n;
+  }
 };
 
 // one patient: parse on host threads into pinned memory, one GPU call per group of equal-size slices, export
 void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::string& patient, Pinned& in, Pinned& out, Totals& tot) {
+  PhaseTimer timer;
   const fs::path outdir = fs::path(opt.out) / patient;
   if (opt.do_export || opt.dump_masks) setupOutputDirectory(outdir);
   const std::vector<std::string> files = loadDICOMFilesForPatient(opt.data, patient);
   const int n = (int)files.size();
   tot.total += n;
+  timer.lap(tot.ns_list);
   // the header of every file is parsed from its first bytes; the pixel payload is then read straight into the
   // pinned staging buffer (one copy)
   std::vector<nm03::dicom::FileReader> readers(n);
@@ -202,6 +214,7 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       std::cerr << "Error processing file " << files[i] << ":\nDetailed error: " << e.what() << std::endl;
     }
   });
+  timer.lap(tot.ns_parse);
   nm03_params params;
   nm03_default_params(&params);
   int ok = 0;
@@ -227,11 +240,13 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       std::cerr << "Error processing patient " << patient << ": short read of pixel data" << std::endl;
       continue;
     }
+    timer.lap(tot.ns_read);
     params.input_unsigned = slices[first].pixel_representation == 0;
     nm03_outputs o = {};
     o.dilated = (uint8_t*)out.p;
     std::vector<int> status(m, 0);
     const int rc = nm03_process_batch(ctx, gpu, in.p, m, w, h, &params, nullptr, 0, &o, status.data());
+    timer.lap(tot.ns_gpu);
     if (rc != NM03_OK) {
       std::lock_guard<std::mutex> lk(tot.log);
       for (int j = 0; j < m; ++j)
@@ -254,6 +269,7 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
           std::cerr << "Error in export stage: " << e.what() << std::endl;
         }
       });
+    timer.lap(tot.ns_export);
   }
   tot.ok += ok;
   tot.patients_ok += 1;
@@ -284,10 +300,14 @@ int runBatch(const Options& opt) {
   for (int g = 0; g < (sequential ? 1 : G); ++g) {
     // contiguous patient range of GPU g
     const int lo = sequential ? 0 : (int)((long)g * P / G), hi = sequential ? P : (int)((long)(g + 1) * P / G);
-    const int S = sequential ? 1 : opt.streams;
+    // Feeders per GPU: each takes whole patients and spreads a patient's slices over the shared pool.  Measured on 120
+    // patients x 24 slices in /dev/shm, 16 cores: 3 feeders 21-29k slices/s, 8 feeders 18k, 16 pool-less feeders 8-11k
+    // (every feeder then pins its own staging buffers and reads its 24 files one after the other).
+    const int S = sequential ? 1 : std::max(1, opt.streams);
+    const int inner_threads = opt.host_threads;
     auto next = std::make_shared<std::atomic<int>>(lo);
     for (int s = 0; s < S; ++s)
-      feeders.emplace_back([&, g, hi, next] {
+      feeders.emplace_back([&, g, hi, next, inner_threads] {
         Pinned in, out;
         for (int i; (i = next->fetch_add(1)) < hi;) {
           try {
@@ -297,7 +317,9 @@ int runBatch(const Options& opt) {
               one.host_threads = 1;
               processPatient(ctx, g, one, patients[i], in, out, tot);
             } else {
-              processPatient(ctx, g, opt, patients[i], in, out, tot);
+              Options mine = opt;
+              mine.host_threads = inner_threads;
+              processPatient(ctx, g, mine, patients[i], in, out, tot);
             }
           } catch (const std::exception& e) {
             std::lock_guard<std::mutex> lk(tot.log);
@@ -314,6 +336,9 @@ int runBatch(const Options& opt) {
               "\"slices_per_sec\": %.1f, \"export\": %s}\n",
               opt.mode.c_str(), sequential ? 1 : G, P, tot.total.load(), tot.ok.load(), sec, tot.ok.load() / sec,
               opt.do_export ? "true" : "false");
+  if (std::getenv("NM03_DRIVER_TIMING"))
+    std::fprintf(stderr, "feeder wall time per phase, summed over feeders [ms]: list %.1f, parse %.1f, read %.1f, gpu call %.1f, export %.1f\n",
+                 tot.ns_list / 1e6, tot.ns_parse / 1e6, tot.ns_read / 1e6, tot.ns_gpu / 1e6, tot.ns_export / 1e6);
   nm03_shutdown(ctx);
   return 0;
 }
