@@ -329,7 +329,7 @@ def main():
     real_step = step
 
     def step(i, n_str):   # noqa: F811 - the profiled variant of the same call
-        ctx.profile_enable(i % PROFILE_EVERY == 0)
+        ctx.profile_enable((i - args.warmup) % PROFILE_EVERY == 0)   # the first step of the region is always sampled
         real_step(i, n_str)
 
     serial_ms = timed_region(serial_steps, 1)
