@@ -206,7 +206,9 @@ def driver_io_figure():
             for name, extra in (("dicom_to_mask", ["--no-export"]), ("dicom_to_jpeg", [])):
                 r = subprocess.run([drv, "--data", td + "/d", "--out", td + "/o", "--gpus", "0"] + extra, capture_output=True,
                                    text=True, timeout=300)
-                out[name + "_slices_per_sec"] = json.loads(r.stdout.strip().splitlines()[-1])["slices_per_sec"]
+                rep = json.loads(r.stdout.strip().splitlines()[-1])
+                out[name + "_slices_per_sec"] = rep["slices_per_sec"]
+                out[name + "_startup_seconds"] = rep.get("startup_seconds")   # context, pinned ring, kernel load: not in the rate
             out["sample"] = f"20 patients x {SLICES} slices {W}x{H} (BASELINE configs[2]), DICOM files in a temp dir, timed after context start-up"
             return out
     except Exception as e:  # informational only
