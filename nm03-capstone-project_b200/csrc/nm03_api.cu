@@ -53,8 +53,8 @@ const bool g_force_exact = [] { const char* e = getenv("NM03_FORCE_EXACT_SHARPEN
 struct Slot {
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;     // recorded after the last use of this slot's scratch
-  bool used = false;
-  cudaStream_t last_stream = nullptr;  // the stream `done` was last recorded on
+  std::atomic<bool> used{false};
+  std::atomic<cudaStream_t> last_stream{nullptr};  // the stream `done` was last recorded on (both read by other callers' slots)
   uint32_t* pred = nullptr;       // scratch: predicate bit-plane [n][h][wpr]
   size_t pred_bytes = 0;
   void* stage_in = nullptr;       // scratch: device copy of host inputs
@@ -149,6 +149,18 @@ struct SlotLease {
 int order_after_last_use(Slot* s, cudaStream_t st) {
   if (s->used && s->last_stream != st) CK(cudaStreamWaitEvent(st, s->done, 0));
   return NM03_OK;
+}
+
+// Is a batch that was queued through another slot, on another stream, still running on this GPU?
+bool others_in_flight(Worker* wk, const Slot* mine, cudaStream_t st) {
+  for (auto& o : wk->slots) {
+    if (&o == mine || !o.used.load(std::memory_order_relaxed) || o.last_stream.load(std::memory_order_relaxed) == st) continue;
+    if (cudaEventQuery(o.done) == cudaErrorNotReady) {
+      (void)cudaGetLastError();   // "not ready" is an answer, not a failure: keep it out of the next launch check
+      return true;
+    }
+  }
+  return false;
 }
 
 int mark_used(Slot* s, cudaStream_t st) {
@@ -361,7 +373,7 @@ int se_halfwidths(int size, int se_shape, int* n_out, int8_t* hw) {
 
 // cluster size: the smallest power of two whose per-CTA planes fit in shared memory, widened while
 // the batch alone cannot fill the 148 SMs
-int pick_cluster(int n, int h, int wpr, int* rows_per) {
+int pick_cluster(int n, int h, int wpr, int* rows_per, bool throughput) {
   const size_t cap = 200 * 1024;
   int c = 1;
   for (;; c *= 2) {
@@ -376,7 +388,11 @@ int pick_cluster(int n, int h, int wpr, int* rows_per) {
       return 0;
     }
   }
-  while (c < nm03::SEG_MAX_CLUSTER && n * c * 2 <= 148 && (h + 2 * c - 1) / (2 * c) >= 32) c *= 2;
+  // A wider cluster shortens the fill of a batch that has the GPU to itself (24 slices 512x512: 27 us with 4 CTAs per
+  // slice, 35 us with one).  When other batches are in flight on other streams the latency is hidden anyway and what
+  // counts is how many SM slots the clusters take away from their K1: then the smallest cluster that fits is kept
+  // (4 streams x 24 slices: 438 000 slices/s with 1 CTA per slice, 411 000 with 4).
+  while (!throughput && c < nm03::SEG_MAX_CLUSTER && n * c * 2 <= 148 && (h + 2 * c - 1) / (2 * c) >= 32) c *= 2;
   if (g_force_cluster > 0) {  // NM03_CLUSTER: tuning override (must still fit)
     int cc = g_force_cluster;
     if ((cc == 1 || cc == 2 || cc == 4 || cc == 8) && nm03::seg_smem_bytes((h + cc - 1) / cc, wpr) <= cap && (h + cc - 1) / cc >= nm03::SEG_HALO) c = cc;
@@ -386,11 +402,11 @@ int pick_cluster(int n, int h, int wpr, int* rows_per) {
 }
 
 int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, const int* seeds_xy, int n_seeds,
-             bool do_fill) {
+             bool do_fill, bool throughput = false) {
   memset(&k, 0, sizeof(k));
   k.w = w; k.h = h; k.n = n; k.wpr = (w + 31) / 32;
   int rows = 0;
-  const int c = pick_cluster(n, h, k.wpr, &rows);
+  const int c = pick_cluster(n, h, k.wpr, &rows, throughput);
   if (c < 0) return c;
   k.cluster = c;
   k.rows_per = rows;
@@ -488,14 +504,14 @@ int ensure_lut(Worker* wk, Slot* s, cudaStream_t st, nm03::PreParams& pre) {
 
 // queue K1 + K23 for n device-resident slices on `st`
 int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h,
-                     const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out) {
+                     const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out, bool resident_caller) {
   int rc, hs = 0;
   if ((rc = check_params(p, w, h, true))) return rc;
   if ((rc = check_preprocess(p, &hs))) return rc;
   nm03::PreParams pre;
   if ((rc = fill_pre(pre, p, n, w, h, hs))) return rc;
   nm03::SegParams seg;
-  if ((rc = fill_seg(seg, p, n, w, h, seeds_xy, n_seeds, true))) return rc;
+  if ((rc = fill_seg(seg, p, n, w, h, seeds_xy, n_seeds, true, resident_caller && others_in_flight(wk, s, st)))) return rc;
   if ((rc = se_halfwidths(p->dilate_size, p->se_shape, &seg.dil_n, seg.dil_hw))) return rc;
   if (p->erode_size > 0 && d_out->eroded) {
     if ((rc = se_halfwidths(p->erode_size, p->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
@@ -801,7 +817,7 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
   DeviceGuard g(wk->device);
   SlotLease lease(wk, (cudaStream_t)stream);
   cudaStream_t st = stream ? (cudaStream_t)stream : lease.s->stream;
-  return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out);
+  return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out, true);
 }
 
 int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
@@ -858,7 +874,8 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
     if (out->sharpened) d.sharpened = (float*)(so + o_sh);
     if (out->median) d.median = (float*)(so + o_med);
     if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
-    rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d);
+    // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
+    rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, false);
     if (rc) { result = rc; break; }
 #define NM03_D2H(field, off, elem)                                                                          \
   if (out->field && e == cudaSuccess)                                                                       \
