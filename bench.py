@@ -300,12 +300,16 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    issue_s = [0.0]
+
     def timed_region(steps, n_str):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record(stream)                      # every stream is idle here (barrier synchronised the device)
+        t_issue = time.perf_counter()
         for i in range(steps):
             step(args.warmup + i, n_str)
+        issue_s[0] = time.perf_counter() - t_issue   # host time spent queueing the steps (must stay below the device time)
         for other in streams[1:n_str]:
             stream.wait_stream(other)          # e1 fires after the last step of every stream
         e1.record(stream)
@@ -320,6 +324,7 @@ def main():
     sampler.start()
     launches0 = ctx.kernel_launches()
     ms = timed_region(args.steps, n_streams)
+    issue_ms_per_step = issue_s[0] * 1e3 / args.steps
     launches = ctx.kernel_launches() - launches0
 
     # Per-kernel durations for the roofline: the same steps once more on ONE stream, where a kernel's CUDA-event
@@ -413,7 +418,8 @@ def main():
         cpu_val, reps, cpu_dt = time_cpu(oracle, h_in[0].copy(), threads, args.cpu_seconds, 1000)
         line = {
             "metric": METRIC, "value": world * args.steps * SLICES / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "host_issue_ms_per_step": issue_ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "s16x2 min/max + f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "slices_per_step_per_gpu": SLICES, "parallelism": f"patient-range x{world}",
                        "l2": f"rotating {N_SERIES} distinct resident series ({N_SERIES * SLICES * W * H * 2 >> 20} MiB > 126 MB L2)",
