@@ -379,7 +379,12 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     for (int r = 0; r < K; ++r)
 #pragma unroll
       for (int c = 0; c < RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
+#ifdef NM03_TUNE_SKIP_B   // tuning builds only (tools/README.md): the window centre instead of the median
+#pragma unroll
+    for (int i = 0; i < RUN; ++i) o[i] = v[i + R][R];
+#else
     MedianRun<K>::run(v, o);
+#endif
     float lo[RUN], hi[RUN];
     if (p.lut) {
 #pragma unroll
@@ -489,6 +494,13 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     constexpr int HE = MODE == K1_FAST_HE2 ? 2 : HS;
     constexpr int NT = 2 * HE + 1;
     constexpr int RB = (HE > 2) ? 4 : 8;        // output rows per thread (fewer with the wide kernel: registers)
+#ifdef NM03_TUNE_SKIP_C   // tuning builds only: no sharpen/predicate work, an all-zero predicate plane
+    for (int it = tid; it < K1_TH * 4; it += K1_THREADS) {
+      const int oy = y0 + (it >> 2), wi = (x0 >> 5) + (it & 3);
+      if (p.predicate && oy < h && wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = 0u;
+    }
+    if (false)
+#endif
     for (int it = tid; it < (K1_TH / RB) * (K1_TW / 4); it += K1_THREADS) {
       const int band = it / (K1_TW / 4), xq = it - band * (K1_TW / 4);
       const int oyl0 = band * RB;
