@@ -227,6 +227,9 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   int slice, x0, y0;
   decode(blk, slice, x0, y0);
   const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
+  // the next work item is asked for now and used after phase A: the counter's round trip to L2 stays off the critical path
+  int fetched = 0;
+  if (tid == 0) fetched = fetch(blk);
 
   // ---- phase A: raw halo tile -> packed keys --------------------------------------------------
   const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
@@ -302,7 +305,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       P[idx] = a | (b << 16);
     }
   }
-  if (tid == 0) s_next = fetch(blk);   // the previous value of s_next was read by everybody before the last barrier
+  if (tid == 0) s_next = fetched;   // the previous value of s_next was read by everybody before the last barrier
   __syncthreads();
   const int next_blk = s_next;
   if (p.use_tma && tid == 0 && next_blk < total_blocks) issue_tma(next_blk);  // T is free again
