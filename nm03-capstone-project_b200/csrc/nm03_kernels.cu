@@ -12,6 +12,7 @@
 // places where rounding must follow the oracle use explicit _rn intrinsics.
 #include "nm03_device.h"
 
+#include <cstdio>
 #include <cstring>
 
 #include <cooperative_groups.h>
@@ -161,6 +162,13 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 
+#ifdef NM03_TUNE_STAMPS   // tuning builds only: thread 0's clock per phase, summed over all work items of the process
+__device__ unsigned long long g_stamps[12];
+#define NM03_STAMP(i) do { if (tid == 0) { const long long t_ = clock64(); atomicAdd(&g_stamps[i], (unsigned long long)(t_ - t_prev)); t_prev = t_; } } while (0)
+#else
+#define NM03_STAMP(i) do { } while (0)
+#endif
+
 template <int K, int HS, int MODE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p,
                                                                          const __grid_constant__ CUtensorMap tmap) {
@@ -203,9 +211,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   auto fetch = [&](int prev) -> int {   // one thread
     return p.sched ? (int)atomicAdd(&p.sched[0], 1u) : prev + (int)gridDim.x;
   };
-  auto issue_tma = [&](int blk) {       // one thread: bulk tensor copy of the raw halo tile of work item blk
-    int s_, x_, y_;
-    decode(blk, s_, x_, y_);
+  // decode() divides by run-time values; thread 0 does it once per work item, one item ahead, and hands the result
+  // to the CTA through shared memory (done by every thread it cost ~1900 cycles per item on the uniform datapath)
+  __shared__ int s_dec[2][4];
+  auto issue_tma = [&](int s_, int x_, int y_) {   // one thread: bulk tensor copy of the raw halo tile of a work item
     mbar_expect_tx(&bar, RH * K1_PWS * 2);
     tma_load_3d(T, &tmap, &bar, x_ - 8, y_ - K1_HS_MAX - R, s_);
   };
@@ -216,16 +225,21 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
 
   if (tid == 0) {
     if (p.use_tma) mbar_init(&bar, 1);
-    s_next = p.sched ? (int)atomicAdd(&p.sched[0], 1u) : (int)blockIdx.x;
+    const int first = p.sched ? (int)atomicAdd(&p.sched[0], 1u) : (int)blockIdx.x;
+    s_next = first;
+    if (first < total_blocks) decode(first, s_dec[0][0], s_dec[0][1], s_dec[0][2]);
   }
   __syncthreads();
   int blk = s_next;
   __syncthreads();   // s_next is rewritten inside the loop: everybody must have read the first value
-  if (p.use_tma && tid == 0 && blk < total_blocks) issue_tma(blk);
+  if (p.use_tma && tid == 0 && blk < total_blocks) issue_tma(s_dec[0][0], s_dec[0][1], s_dec[0][2]);
 
   for (int iter = 0; blk < total_blocks; ++iter) {
-  int slice, x0, y0;
-  decode(blk, slice, x0, y0);
+#ifdef NM03_TUNE_STAMPS
+  long long t_prev = clock64();
+  if (tid == 0) atomicAdd(&g_stamps[11], 1ull);
+#endif
+  const int slice = s_dec[iter & 1][0], x0 = s_dec[iter & 1][1], y0 = s_dec[iter & 1][2];
   const uint16_t* __restrict__ img = reinterpret_cast<const uint16_t*>(p.in) + (size_t)slice * w * h;
   // the next work item is asked for now and used after phase A: the counter's round trip to L2 stays off the critical path
   int fetched = 0;
@@ -236,13 +250,16 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   if (p.use_tma) {
     // The (MH+2R) x 144 int16 halo tile arrives in shared memory by one bulk tensor copy; rows/columns
     // outside the image arrive as zeros.
+    NM03_STAMP(9);
     mbar_wait(&bar, iter & 1);
+    NM03_STAMP(0);
     const bool interior = gx0 >= 0 && gy0 >= 0 && gx0 + RW <= w && gy0 + RH <= h;
     if (!p.border_zero) {
       // 4 packed words per thread: pixels i..i+3 of row q (low halves) and of row q+36 (high halves);
       // the OFF-pixel shift is folded into the byte permutes
       const uint32_t bias2 = bias | (bias << 16);
       const uint32_t* Tw = reinterpret_cast<const uint32_t*>(T);
+#pragma unroll 3
       for (int idx = tid; idx < PR * (K1_PWS / 4); idx += K1_THREADS) {
         const int q = idx / (K1_PWS / 4), c4 = idx - q * (K1_PWS / 4);
         const int w0 = (4 * c4 + OFF) >> 1;                 // first 32-bit word holding pixel 4*c4 + OFF
@@ -305,11 +322,17 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       P[idx] = a | (b << 16);
     }
   }
+  NM03_STAMP(1);
   if (tid == 0) s_next = fetched;   // the previous value of s_next was read by everybody before the last barrier
   __syncthreads();
   const int next_blk = s_next;
-  if (p.use_tma && tid == 0 && next_blk < total_blocks) issue_tma(next_blk);  // T is free again
+  if (tid == 0 && next_blk < total_blocks) {   // nobody waits for this: the others go on with the skip list
+    int* d = s_dec[(iter + 1) & 1];            // read at the top of the next iteration, many barriers from here
+    decode(next_blk, d[0], d[1], d[2]);
+    if (p.use_tma) issue_tma(d[0], d[1], d[2]);   // T is free again
+  }
 
+  NM03_STAMP(2);
   // ---- phase B: median of the K x K window on packed keys, then f() ---------------------------
   // Work items (packed row, run of 8 columns).  An item whose whole input footprint lies at or below
   // the clip floor has a known result (skip_val) and is not sorted: 8x8-block maxima of the packed
@@ -319,22 +342,38 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   __shared__ int n_work;
   if (p.skip_on) {
     if (tid == 0) n_work = 0;
-    for (int bidx = tid; bidx < ((PR + 7) / 8) * (K1_PWS / 8); bidx += K1_THREADS) {
+    constexpr int NBLK = ((PR + 7) / 8) * (K1_PWS / 8);
+    for (int base = 0; base < 2 * NBLK; base += K1_THREADS) {   // two threads per 8x8 block, four rows each (block-uniform trips)
+      const int bidx = (base + tid) >> 1, half = tid & 1;
       const int g = bidx / (K1_PWS / 8), c8 = bidx - g * (K1_PWS / 8);
       uint32_t m = 0x80008000u;  // (-32768, -32768)
-      for (int q = 8 * g; q < min(PR, 8 * g + 8); ++q) {
-        const uint4 a = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8);
-        const uint4 c = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8 + 4);
-        m = __vimax3_s16x2(m, __vmaxs2(a.x, a.y), __vmaxs2(a.z, a.w));
-        m = __vimax3_s16x2(m, __vmaxs2(c.x, c.y), __vmaxs2(c.z, c.w));
+      if (bidx < NBLK) {
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          const int q = 8 * g + 4 * half + qq;
+          if (q < PR) {
+            const uint4 a = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8);
+            const uint4 c = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8 + 4);
+            m = __vimax3_s16x2(m, __vmaxs2(a.x, a.y), __vmaxs2(a.z, a.w));
+            m = __vimax3_s16x2(m, __vmaxs2(c.x, c.y), __vmaxs2(c.z, c.w));
+          }
+        }
       }
-      blkmax[g][c8] = m;
+      m = __vmaxs2(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      if (bidx < NBLK && half == 0) blkmax[g][c8] = m;
     }
     __syncthreads();
+    NM03_STAMP(10);
     const int lane = tid & 31;
-    for (int base = 0; base < K1_MHP * NRUN; base += K1_THREADS) {   // trip count is block-uniform
-      const int it = base + tid;
-      bool need = false;
+    // every thread rates its (up to ROUNDS) items first, then each warp reserves room in the list once
+    constexpr int ROUNDS = (K1_MHP * NRUN + K1_THREADS - 1) / K1_THREADS;
+    uint32_t bal[ROUNDS];
+    bool need[ROUNDS];
+    int total = 0;
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+      const int it = r * K1_THREADS + tid;
+      need[r] = false;
       if (it < K1_MHP * NRUN) {
         const int prow = it / NRUN, run = it - prow * NRUN;
         // footprint: packed rows prow .. prow+K-1, columns run*RUN .. run*RUN + RUN+K-2
@@ -344,8 +383,8 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         const uint32_t m = __vmaxs2(__vmaxs2(blkmax[g0][c0], blkmax[g0][c1]), __vmaxs2(blkmax[g1][c0], blkmax[g1][c1]));
         static_assert(K - 1 <= 8 && (RUN + K - 2) % 8 + 0 >= 0 && RUN + K - 1 <= 16 && (8 % RUN == 0 || RUN % 8 == 0),
                       "work item footprint must fit in 2x2 blocks of 8x8 packed words");
-        need = __vmaxs2(m, p.skip_key2) != p.skip_key2;        // some sample above the floor, in either half
-        if (!need) {
+        need[r] = __vmaxs2(m, p.skip_key2) != p.skip_key2;        // some sample above the floor, in either half
+        if (!need[r]) {
           float* mlo = M + prow * K1_MW + run * RUN;
           const float4 f4 = make_float4(p.skip_val, p.skip_val, p.skip_val, p.skip_val);
 #pragma unroll
@@ -364,14 +403,20 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
           }
         }
       }
-      const uint32_t bal = __ballot_sync(0xffffffffu, need);
-      int slot = 0;
-      if (lane == 0 && bal) slot = atomicAdd(&n_work, __popc(bal));
-      slot = __shfl_sync(0xffffffffu, slot, 0);
-      if (need) worklist[slot + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)it;
+      bal[r] = __ballot_sync(0xffffffffu, need[r]);
+      total += __popc(bal[r]);
+    }
+    int slot = 0;
+    if (lane == 0 && total) slot = atomicAdd(&n_work, total);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+      if (need[r]) worklist[slot + __popc(bal[r] & ((1u << lane) - 1u))] = (uint16_t)(r * K1_THREADS + tid);
+      slot += __popc(bal[r]);
     }
     __syncthreads();
   }
+  NM03_STAMP(3);
   const int n_items = p.skip_on ? n_work : K1_MHP * NRUN;
   for (int wi = tid; wi < n_items; wi += K1_THREADS) {
     const int it = p.skip_on ? worklist[wi] : wi;
@@ -419,7 +464,9 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       }
     }
   }
+  NM03_STAMP(4);
   __syncthreads();
+  NM03_STAMP(5);
 
   // ---- phase B': the sharpen stage samples the MEDIAN IMAGE with clamp-to-edge (or zero), so
   // median-tile entries whose coordinates fall outside the image are replaced (not recomputed from
@@ -446,6 +493,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     __syncthreads();
   }
 
+  NM03_STAMP(6);
   // ---- phase C: unsharp mask, range predicate, stores ------------------------------------------
   const int lane = tid & 31;
   if (MODE == K1_EXACT) {
@@ -529,23 +577,28 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
 #pragma unroll
       for (int r = 0; r < RB; ++r) {
         const int oy = y0 + oyl0 + r;
-        uint32_t nib = 0;
+        uint32_t nib = 0, unc = 0;
 #pragma unroll
         for (int j = 3; j >= 0; --j) {   // pixel 3 first: each sign bit is shifted in below the previous ones
           float blur = 0.0f;
 #pragma unroll
           for (int t = 0; t < NT; ++t) blur = __fmaf_rn(p.gx[t + (K1_HS_MAX - HE)], hsum[r + t][j], blur);
           const float v = cv[r][j];
-          float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
+          const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
           const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
           // signed distance to the interval: negative inside; decided by its sign unless it lies in the band
-          float d = __fsub_rn(fabsf(__fsub_rn(sv, p.rg_mid)), p.rg_half);
-          if (fabsf(d) <= eps) {
-            const float be = blur1_exact<HS>(M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX, p);
-            sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, be)));
-            d = (sv >= p.rg_min && sv <= p.rg_max) ? -1.0f : 1.0f;
-          }
+          const float d = __fsub_rn(fabsf(__fsub_rn(sv, p.rg_mid)), p.rg_half);
           nib = __funnelshift_l(__float_as_uint(d), nib, 1);
+          unc = (unc << 1) | (fabsf(d) <= eps ? 1u : 0u);
+        }
+        if (unc) {   // rare: pixels inside the band are redone in the oracle's exact order, off the straight-line path
+          for (int j = 0; j < 4; ++j)
+            if (unc >> j & 1u) {
+              const float* mc = M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX;
+              const float v = *mc;
+              const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur1_exact<HS>(mc, p))));
+              nib = (sv >= p.rg_min && sv <= p.rg_max) ? (nib | (1u << j)) : (nib & ~(1u << j));
+            }
         }
         nib &= xmask;
         uint32_t word = nib << (4 * (lane & 7));
@@ -564,13 +617,24 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       }
     }
   }
+  NM03_STAMP(7);
   __syncthreads();   // everybody is done with this item (and has read s_next) before the next one starts
+  NM03_STAMP(8);
   blk = next_blk;
   }  // persistent loop over work items
   // the last CTA to leave resets the work counter for the next launch that uses it
   if (p.sched && tid == 0) {
     __threadfence();
-    if (atomicAdd(&p.sched[1], 1u) == gridDim.x - 1) { p.sched[0] = 0u; p.sched[1] = 0u; __threadfence(); }
+    if (atomicAdd(&p.sched[1], 1u) == gridDim.x - 1) {
+      p.sched[0] = 0u; p.sched[1] = 0u; __threadfence();
+#ifdef NM03_TUNE_STAMPS
+      if (p.n >= 400) {
+        const double n = (double)g_stamps[11];
+        printf("K1 cycles per work item (thread 0): decode %.0f tma-wait %.0f pack %.0f next+sync %.0f blkmax %.0f worklist %.0f B %.0f B-barrier %.0f B' %.0f C %.0f end-barrier %.0f (items %.0f)\n",
+               g_stamps[9] / n, g_stamps[0] / n, g_stamps[1] / n, g_stamps[2] / n, g_stamps[10] / n, g_stamps[3] / n, g_stamps[4] / n, g_stamps[5] / n, g_stamps[6] / n, g_stamps[7] / n, g_stamps[8] / n, n);
+      }
+#endif
+    }
   }
 }
 
