@@ -544,7 +544,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     // fast value lies within the proven error bound of a threshold is redone exactly.
     constexpr int HE = MODE == K1_FAST_HE2 ? 2 : HS;
     constexpr int NT = 2 * HE + 1;
-    constexpr int RB = (HE > 2) ? 4 : 8;        // output rows per thread (fewer with the wide kernel: registers)
+    constexpr int RB = 4;                       // output rows per thread (8 rows: fewer FFMAs but more code and registers; 918 vs 932 us at 480 slices)
 #ifdef NM03_TUNE_SKIP_C   // tuning builds only: no sharpen/predicate work, an all-zero predicate plane
     for (int it = tid; it < K1_TH * 4; it += K1_THREADS) {
       const int oy = y0 + (it >> 2), wi = (x0 >> 5) + (it & 3);
