@@ -70,6 +70,32 @@ cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+// NM03_K1_WS=1 selects the warp-specialised K1 (k1_ws) where it applies
+static const bool g_k1_ws = [] { const char* e = getenv("NM03_K1_WS"); return e && e[0] == '1'; }();
+
+// NW consecutive packed words of one tile row -> registers, with the widest shared-memory loads the alignment of a
+// run allows (a run starts every RUN words: 16-byte loads when RUN % 4 == 0, 8-byte loads when RUN is even)
+template <int NW, int RUN_, int K_>
+__device__ __forceinline__ void load_window_row(const uint32_t* __restrict__ src, uint32_t (&v)[NW][K_], int r) {
+  int c = 0;
+  if constexpr (RUN_ % 4 == 0) {
+#pragma unroll
+    for (; c + 4 <= NW; c += 4) {
+      const uint4 q = *reinterpret_cast<const uint4*>(src + c);
+      v[c][r] = q.x; v[c + 1][r] = q.y; v[c + 2][r] = q.z; v[c + 3][r] = q.w;
+    }
+  }
+  if constexpr (RUN_ % 2 == 0) {
+#pragma unroll
+    for (; c + 2 <= NW; c += 2) {
+      const uint2 q = *reinterpret_cast<const uint2*>(src + c);
+      v[c][r] = q.x; v[c + 1][r] = q.y;
+    }
+  }
+#pragma unroll
+  for (; c < NW; ++c) v[c][r] = src[c];
+}
+
 template <int K>
 struct MedianRun;
 #define NM03_DEFINE_MEDIAN_RUN(K_)                                                                              \
@@ -424,9 +450,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     uint32_t v[RUN + K - 1][K], o[RUN];
     const uint32_t* src = P + prow * K1_PWS + run * RUN;
 #pragma unroll
-    for (int r = 0; r < K; ++r)
-#pragma unroll
-      for (int c = 0; c < RUN + K - 1; ++c) v[c][r] = src[r * K1_PWS + c];
+    for (int r = 0; r < K; ++r) load_window_row<RUN + K - 1, RUN, K>(src + r * K1_PWS, v, r);
 #ifdef NM03_TUNE_SKIP_B   // tuning builds only (tools/README.md): the window centre instead of the median
 #pragma unroll
     for (int i = 0; i < RUN; ++i) o[i] = v[i + R][R];
@@ -638,6 +662,429 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   }
 }
 
+// =================================================================================================
+// K1, warp-specialised variant (fast predicate modes, TMA staging, clamp border)
+// =================================================================================================
+// One CTA per SM, three groups of warps that work on different tiles at the same time:
+//   loader  (4 warps): raw TMA tile -> packed keys, block maxima, list of windows that need sorting
+//   median  (8 warps): the min/max network and f() -> median tile (the only group that needs many registers)
+//   sharpen (8 warps): border composition, separable unsharp mask, predicate bits -> global memory
+// Packed-key, median and raw tiles are double-buffered; full/empty mbarriers pass them between the groups.
+// In k1_preprocess the same three phases run one after the other in every CTA: the median phase keeps the
+// min/max pipe busy with 8 warps, the other two are latency-bound and leave that pipe idle.
+constexpr int WS_B_WARPS = 8, WS_P_WARPS = 4, WS_C_WARPS = 8;
+constexpr int WS_B_THREADS = 32 * WS_B_WARPS, WS_P_THREADS = 32 * WS_P_WARPS, WS_C_THREADS = 32 * WS_C_WARPS;
+constexpr int WS_THREADS = WS_B_THREADS + WS_P_THREADS + WS_C_THREADS;   // 640
+constexpr int WS_RING = 8;         // work-item descriptors in flight (the loader runs at most 4 items ahead of the sharpen group)
+constexpr int WS_REGS_B = 136, WS_REGS_P = 56, WS_REGS_C = 72;   // 256*136 + 128*56 + 256*72 <= 640*96
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void group_bar(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+#ifdef NM03_TUNE_STAMPS
+__device__ unsigned long long g_ws_stamps[8];
+#define WS_STAMP(cond, i) do { if (cond) { const long long t_ = clock64(); atomicAdd(&g_ws_stamps[i], (unsigned long long)(t_ - ws_prev)); ws_prev = t_; } } while (0)
+#else
+#define WS_STAMP(cond, i) do { } while (0)
+#endif
+
+template <int K>
+constexpr size_t ws_smem_bytes() {
+  constexpr int R = K / 2;
+  return 2 * ((((size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 127) / 128) * 128 + (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 +
+              (size_t)((K1_MHP * (K1_MW / MedianRun<K>::RUN) * 2 + 15) / 16) * 16) + 128;
+}
+
+template <int K, int HS, int MODE>
+__global__ void __launch_bounds__(WS_THREADS, 1) k1_ws(const __grid_constant__ PreParams p, const __grid_constant__ CUtensorMap tmap) {
+  constexpr int R = K / 2;
+  constexpr int PR = K1_MHP + 2 * R;
+  constexpr int RW = K1_MW + 2 * R;
+  constexpr int RUN = MedianRun<K>::RUN;
+  constexpr int NRUN = K1_MW / RUN;
+  constexpr int NITEMS = K1_MHP * NRUN;
+  constexpr int RH = K1_MH + 2 * R;
+  constexpr int OFF = 8 - K1_HS_MAX - R;
+  static_assert(RW + OFF <= K1_PWS && OFF >= 0, "halo does not fit the aligned TMA box");
+  static_assert(MODE != K1_EXACT, "the warp-specialised kernel implements the fast predicate modes only");
+
+  extern __shared__ __align__(16) uint32_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  constexpr size_t T_BYTES = (((size_t)RH * K1_PWS * 2 + 127) / 128) * 128, P_BYTES = (size_t)PR * K1_PWS * 4, M_BYTES = (size_t)K1_MH * K1_MW * 4;
+  constexpr size_t W_BYTES = (size_t)((NITEMS * 2 + 15) / 16) * 16;
+  static_assert(T_BYTES % 128 == 0 && P_BYTES % 16 == 0 && M_BYTES % 16 == 0, "tile buffers must keep their alignment");
+  // buffer b of each kind (computed, not looked up: an indexed pointer array would live in local memory)
+  auto Tbuf = [&](int b) { return reinterpret_cast<uint16_t*>(base + b * T_BYTES); };
+  auto Pbuf = [&](int b) { return reinterpret_cast<uint32_t*>(base + 2 * T_BYTES + b * P_BYTES); };
+  auto Mbuf = [&](int b) { return reinterpret_cast<float*>(base + 2 * T_BYTES + 2 * P_BYTES + b * M_BYTES); };
+  auto Wbuf = [&](int b) { return reinterpret_cast<uint16_t*>(base + 2 * (T_BYTES + P_BYTES + M_BYTES) + b * W_BYTES); };
+  __shared__ __align__(8) uint64_t bar_tma[2], bar_pfull[2], bar_pempty[2], bar_mfull[2], bar_mempty[2];
+  __shared__ int s_dec[WS_RING][4];   // slice, x0, y0, valid
+  __shared__ int s_nwork[2], s_nskip[2];
+  __shared__ uint32_t blkmax[(PR + 7) / 8][K1_PWS / 8];
+
+  const int tid = threadIdx.x;
+  const int w = p.w, h = p.h;
+  const uint32_t bias = p.input_unsigned ? 0x8000u : 0u;
+  const int total_blocks = p.n * p.tiles_x * p.tiles_y;
+#ifdef NM03_TUNE_STAMPS
+  long long ws_prev = clock64();
+#endif
+
+  cudaTriggerProgrammaticLaunchCompletion();   // as in k1_preprocess: lets K23's CTAs become resident while this grid drains
+  if (tid == 0) {
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&bar_tma[b], 1);
+      mbar_init(&bar_pfull[b], WS_P_THREADS);
+      mbar_init(&bar_pempty[b], WS_B_THREADS);
+      mbar_init(&bar_mfull[b], WS_B_THREADS);
+      mbar_init(&bar_mempty[b], WS_C_THREADS);
+    }
+  }
+  __syncthreads();
+
+  if (tid >= WS_B_THREADS && tid < WS_B_THREADS + WS_P_THREADS) {
+    // ================= loader group =================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(WS_REGS_P));
+    const int t = tid - WS_B_THREADS, warp = t >> 5, ln = t & 31;
+    auto decode = [&](int blk, int* d) {   // work item -> slice, tile origin (central tiles first, see PreParams::tile_order)
+      int tile_;
+      if (p.tile_order_on) { d[0] = blk % p.n; tile_ = p.tile_order[blk / p.n]; }
+      else { tile_ = blk % (p.tiles_x * p.tiles_y); d[0] = blk / (p.tiles_x * p.tiles_y); }
+      d[1] = (tile_ % p.tiles_x) * K1_TW;
+      d[2] = (tile_ / p.tiles_x) * K1_TH;
+    };
+    auto announce = [&](int i, int blk) {   // leader: descriptor of item i, and its raw tile on the way
+      int* d = s_dec[i % WS_RING];
+      d[3] = blk < total_blocks;
+      if (d[3]) {
+        decode(blk, d);
+        mbar_expect_tx(&bar_tma[i & 1], RH * K1_PWS * 2);
+        tma_load_3d(Tbuf(i & 1), &tmap, &bar_tma[i & 1], d[1] - 8, d[2] - K1_HS_MAX - R, d[0]);
+      }
+    };
+    int blk = 0;
+    if (t == 0) {
+      blk = p.sched ? (int)atomicAdd(&p.sched[0], 1u) : (int)blockIdx.x;
+      announce(0, blk);
+    }
+    group_bar(1, WS_P_THREADS);
+    for (int i = 0;; ++i) {
+      const int b = i & 1, n = i >> 1;
+      const int* d = s_dec[i % WS_RING];
+      // (a full/empty barrier must never run two phases ahead of its waiters, so even the end marker waits its turn)
+      if (n >= 1) mbar_wait(&bar_pempty[b], (n - 1) & 1);   // the median group is done with this packed buffer
+      if (!d[3]) { mbar_arrive(&bar_pfull[b]); break; }     // no more work: the end marker travels down the pipeline
+      const int x0 = d[1], y0 = d[2];
+      if (t == 0) {   // next item: its raw buffer was last read while item i-1 was packed (a group barrier ago)
+        blk = p.sched ? (int)atomicAdd(&p.sched[0], 1u) : blk + (int)gridDim.x;
+        announce(i + 1, blk);
+      }
+      WS_STAMP(t == 0, 0);    // descriptor, next-item bookkeeping, wait for the median group's release
+      mbar_wait(&bar_tma[b], n & 1);
+      WS_STAMP(t == 0, 1);    // wait for the raw tile
+      const uint16_t* T = Tbuf(b);
+      uint32_t* P = Pbuf(b);
+      const int gx0 = x0 - K1_HS_MAX - R, gy0 = y0 - K1_HS_MAX - R;
+      {
+        // 4 packed words per step: pixels i..i+3 of row q (low halves) and of row q+36 (high halves);
+        // the OFF-pixel shift is folded into the byte permutes (same code as k1_preprocess)
+        const uint32_t bias2 = bias | (bias << 16);
+        const uint32_t* Tw = reinterpret_cast<const uint32_t*>(T);
+#pragma unroll 3
+        for (int idx = t; idx < PR * (K1_PWS / 4); idx += WS_P_THREADS) {
+          const int q = idx / (K1_PWS / 4), c4 = idx - q * (K1_PWS / 4);
+          const int w0 = (4 * c4 + OFF) >> 1;
+          const uint32_t* ra = Tw + q * (K1_PWS / 2) + w0;
+          const uint32_t* rb = Tw + (q + K1_MHP) * (K1_PWS / 2) + w0;
+          const bool last = w0 + 2 >= K1_PWS / 2;
+          const uint32_t a0 = ra[0], a1 = ra[1], a2 = last ? 0u : ra[2];
+          const uint32_t b0 = rb[0], b1 = rb[1], b2 = last ? 0u : rb[2];
+          uint4 o;
+          if ((OFF & 1) == 0) {
+            o.x = __byte_perm(a0, b0, 0x5410); o.y = __byte_perm(a0, b0, 0x7632);
+            o.z = __byte_perm(a1, b1, 0x5410); o.w = __byte_perm(a1, b1, 0x7632);
+          } else {
+            o.x = __byte_perm(a0, b0, 0x7632); o.y = __byte_perm(a1, b1, 0x5410);
+            o.z = __byte_perm(a1, b1, 0x7632); o.w = __byte_perm(a2, b2, 0x5410);
+          }
+          o.x ^= bias2; o.y ^= bias2; o.z ^= bias2; o.w ^= bias2;
+          *reinterpret_cast<uint4*>(P + q * K1_PWS + 4 * c4) = o;
+        }
+      }
+      if (t == 0) { s_nwork[b] = 0; s_nskip[b] = 0; }
+      group_bar(1, WS_P_THREADS);
+      const bool interior = gx0 >= 0 && gy0 >= 0 && gx0 + RW <= w && gy0 + RH <= h;
+      if (!interior) {
+        // border tile: cells whose samples lie outside the image replicate the image edge (clamp-to-edge)
+        auto key = [&](int col, int row) -> uint32_t {
+          const int gx = gx0 + col, gy = gy0 + row;
+          const int cx = clampi(clampi(gx, 0, w - 1) - gx0 + OFF, 0, K1_PWS - 1), cy = clampi(clampi(gy, 0, h - 1) - gy0, 0, RH - 1);
+          return (T[cy * K1_PWS + cx] ^ bias) & 0xffffu;
+        };
+        const int cl = max(0, -gx0), cr = min(K1_PWS, w - gx0);
+        for (int q = warp; q < PR; q += WS_P_WARPS) {
+          const int gya = gy0 + q, gyb = gya + K1_MHP;
+          if (gya < 0 || gyb >= h || gya >= h || gyb < 0) {
+            for (int col = ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          } else {
+            for (int col = ln; col < cl; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+            for (int col = cr + ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          }
+        }
+        group_bar(1, WS_P_THREADS);
+      }
+      // windows to sort: the front of the list; windows that lie at or below the clip floor: its back
+      uint16_t* wl = Wbuf(b);
+      if (p.skip_on) {
+        constexpr int NBLK = ((PR + 7) / 8) * (K1_PWS / 8);
+        for (int base2 = 0; base2 < 2 * NBLK; base2 += WS_P_THREADS) {   // two threads per 8x8 block, four rows each
+          const int bidx = (base2 + t) >> 1, half = t & 1;
+          const int g = bidx / (K1_PWS / 8), c8 = bidx - g * (K1_PWS / 8);
+          uint32_t m = 0x80008000u;
+          if (bidx < NBLK) {
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+              const int q = 8 * g + 4 * half + qq;
+              if (q < PR) {
+                const uint4 a = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8);
+                const uint4 c = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8 + 4);
+                m = __vimax3_s16x2(m, __vmaxs2(a.x, a.y), __vmaxs2(a.z, a.w));
+                m = __vimax3_s16x2(m, __vmaxs2(c.x, c.y), __vmaxs2(c.z, c.w));
+              }
+            }
+          }
+          m = __vmaxs2(m, __shfl_xor_sync(0xffffffffu, m, 1));
+          if (bidx < NBLK && half == 0) blkmax[g][c8] = m;
+        }
+        group_bar(1, WS_P_THREADS);
+        for (int base2 = 0; base2 < NITEMS; base2 += WS_P_THREADS) {   // trip count is group-uniform
+          const int it = base2 + t;
+          bool need = false;
+          if (it < NITEMS) {
+            const int prow = it / NRUN, run = it - prow * NRUN;
+            const int g0 = prow >> 3, g1 = (prow + K - 1) >> 3;
+            const int c0 = (run * RUN) >> 3, c1 = (run * RUN + RUN + K - 2) >> 3;
+            const uint32_t m = __vmaxs2(__vmaxs2(blkmax[g0][c0], blkmax[g0][c1]), __vmaxs2(blkmax[g1][c0], blkmax[g1][c1]));
+            need = __vmaxs2(m, p.skip_key2) != p.skip_key2;
+          }
+          const bool skip = it < NITEMS && !need;
+          const uint32_t bal = __ballot_sync(0xffffffffu, need), sbal = __ballot_sync(0xffffffffu, skip);
+          int slot = 0, sslot = 0;
+          if (ln == 0 && bal) slot = atomicAdd(&s_nwork[b], __popc(bal));
+          if (ln == 0 && sbal) sslot = atomicAdd(&s_nskip[b], __popc(sbal));
+          slot = __shfl_sync(0xffffffffu, slot, 0);
+          sslot = __shfl_sync(0xffffffffu, sslot, 0);
+          const uint32_t below = (1u << ln) - 1u;
+          if (need) wl[slot + __popc(bal & below)] = (uint16_t)it;
+          if (skip) wl[NITEMS - 1 - (sslot + __popc(sbal & below))] = (uint16_t)it;
+        }
+      } else {
+        for (int it = t; it < NITEMS; it += WS_P_THREADS) wl[it] = (uint16_t)it;
+        if (t == 0) s_nwork[b] = NITEMS;
+      }
+      mbar_arrive(&bar_pfull[b]);
+      WS_STAMP(t == 0, 2);    // pack, border, block maxima, lists
+    }
+  }
+  else if (tid < WS_B_THREADS) {
+    // ================= median group =================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(WS_REGS_B));
+    for (int i = 0;; ++i) {
+      const int b = i & 1, n = i >> 1;
+      mbar_wait(&bar_pfull[b], n & 1);
+      if (n >= 1) mbar_wait(&bar_mempty[b], (n - 1) & 1);   // the sharpen group is done with this median buffer
+      if (!s_dec[i % WS_RING][3]) { mbar_arrive(&bar_mfull[b]); break; }
+      WS_STAMP(tid == 0, 3);  // wait for packed keys and a free median buffer
+      const uint32_t* P = Pbuf(b);
+      float* M = Mbuf(b);
+      const uint16_t* wl = Wbuf(b);
+      const int nw = s_nwork[b];
+      for (int wi = tid; wi < nw; wi += WS_B_THREADS) {
+        const int it = wl[wi];
+        const int prow = it / NRUN, run = it - prow * NRUN;
+        uint32_t v[RUN + K - 1][K], o[RUN];
+        const uint32_t* src = P + prow * K1_PWS + run * RUN;
+#pragma unroll
+        for (int r = 0; r < K; ++r) load_window_row<RUN + K - 1, RUN, K>(src + r * K1_PWS, v, r);
+        MedianRun<K>::run(v, o);
+        float lo[RUN], hi[RUN];
+        if (p.lut) {
+#pragma unroll
+          for (int j = 0; j < RUN; ++j) {
+            lo[j] = __ldg(p.lut + (o[j] & 0xffffu));
+            hi[j] = __ldg(p.lut + (o[j] >> 16));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < RUN; ++j) {
+            lo[j] = key_to_float((int)(short)(o[j] & 0xffffu), p);
+            hi[j] = key_to_float((int)(short)(o[j] >> 16), p);
+          }
+        }
+        float* mlo = M + prow * K1_MW + run * RUN;
+        float* mhi = mlo + K1_MHP * K1_MW;
+        if constexpr (RUN % 4 == 0) {
+#pragma unroll
+          for (int j = 0; j < RUN; j += 4) {
+            *reinterpret_cast<float4*>(mlo + j) = make_float4(lo[j], lo[j + 1], lo[j + 2], lo[j + 3]);
+            *reinterpret_cast<float4*>(mhi + j) = make_float4(hi[j], hi[j + 1], hi[j + 2], hi[j + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < RUN; j += 2) {
+            *reinterpret_cast<float2*>(mlo + j) = make_float2(lo[j], lo[j + 1]);
+            *reinterpret_cast<float2*>(mhi + j) = make_float2(hi[j], hi[j + 1]);
+          }
+        }
+      }
+      for (int wi = tid; wi < NITEMS - nw; wi += WS_B_THREADS) {   // windows at or below the clip floor: known result
+        const int it = wl[NITEMS - 1 - wi];
+        const int prow = it / NRUN, run = it - prow * NRUN;
+        float* mlo = M + prow * K1_MW + run * RUN;
+        float* mhi = mlo + K1_MHP * K1_MW;
+#pragma unroll
+        for (int j = 0; j < RUN; j += 2) {
+          *reinterpret_cast<float2*>(mlo + j) = make_float2(p.skip_val, p.skip_val);
+          *reinterpret_cast<float2*>(mhi + j) = make_float2(p.skip_val, p.skip_val);
+        }
+      }
+      mbar_arrive(&bar_pempty[b]);
+      mbar_arrive(&bar_mfull[b]);
+      WS_STAMP(tid == 0, 4);  // sorting networks, f(), stores
+    }
+  }
+  else {
+    // ================= sharpen group =================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(WS_REGS_C));
+    const int t = tid - WS_B_THREADS - WS_P_THREADS, warp = t >> 5, lane = t & 31;
+    constexpr int HE = MODE == K1_FAST_HE2 ? 2 : HS;
+    constexpr int NT = 2 * HE + 1;
+    constexpr int RB = 2;   // output rows per thread: this group has few registers and is off the critical path
+    for (int i = 0;; ++i) {
+      const int b = i & 1, n = i >> 1;
+      mbar_wait(&bar_mfull[b], n & 1);
+      const int* d = s_dec[i % WS_RING];
+      if (!d[3]) break;
+      WS_STAMP(t == 0, 5);    // wait for a median tile
+      const int slice = d[0], x0 = d[1], y0 = d[2];
+      float* M = Mbuf(b);
+      // the sharpen stage samples the MEDIAN IMAGE with clamp-to-edge: entries outside the image are replaced
+      const int mx0 = x0 - K1_HS_MAX, my0 = y0 - K1_HS_MAX;
+      if (mx0 < 0 || my0 < 0 || mx0 + K1_MW > w || my0 + K1_MH > h) {
+        const int cl = max(0, -mx0), cr = min(K1_MW, w - mx0), rt = max(0, -my0), rb = min(K1_MH, h - my0);
+        auto fill = [&](int my, int mx, int cy) {
+          float val = 0.0f;
+          if (rb > rt && cr > cl) val = M[cy * K1_MW + clampi(mx, cl, cr - 1)];   // reads in-image cells only
+          M[my * K1_MW + mx] = val;                                               // writes outside cells only
+        };
+        for (int my = warp; my < K1_MH; my += WS_C_WARPS) {
+          const int cy = clampi(my, rt, rb - 1);
+          if (my < rt || my >= rb) {
+            for (int mx = lane; mx < K1_MW; mx += 32) fill(my, mx, cy);
+          } else {
+            for (int mx = lane; mx < cl; mx += 32) fill(my, mx, cy);
+            for (int mx = cr + lane; mx < K1_MW; mx += 32) fill(my, mx, cy);
+          }
+        }
+        group_bar(2, WS_C_THREADS);
+      }
+      for (int it = t; it < (K1_TH / RB) * (K1_TW / 4); it += WS_C_THREADS) {
+        const int band = it / (K1_TW / 4), xq = it - band * (K1_TW / 4);
+        const int oyl0 = band * RB;
+        const int ox = x0 + 4 * xq;
+        const uint32_t xmask = ox + 3 < w ? 15u : (ox < w ? (1u << (w - ox)) - 1u : 0u);   // pixels inside the image
+        float hsum[RB + 2 * HE][4], cv[RB][4];
+#pragma unroll
+        for (int ri = 0; ri < RB + 2 * HE; ++ri) {
+          const float* row = M + (oyl0 + K1_HS_MAX - HE + ri) * K1_MW + 4 * xq;
+          const float4 q0 = *reinterpret_cast<const float4*>(row);
+          const float4 q1 = *reinterpret_cast<const float4*>(row + 4);
+          const float4 q2 = *reinterpret_cast<const float4*>(row + 8);
+          const float r12[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float a = 0.0f;
+#pragma unroll
+            for (int tt = 0; tt < NT; ++tt) a = __fmaf_rn(p.gx[tt + (K1_HS_MAX - HE)], r12[K1_HS_MAX + j + tt - HE], a);
+            hsum[ri][j] = a;
+            if (ri >= HE && ri < HE + RB) cv[ri - HE][j] = r12[K1_HS_MAX + j];
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          const int oy = y0 + oyl0 + r;
+          uint32_t nib = 0, unc = 0;
+#pragma unroll
+          for (int j = 3; j >= 0; --j) {   // pixel 3 first: each sign bit is shifted in below the previous ones
+            float blur = 0.0f;
+#pragma unroll
+            for (int tt = 0; tt < NT; ++tt) blur = __fmaf_rn(p.gx[tt + (K1_HS_MAX - HE)], hsum[r + tt][j], blur);
+            const float v = cv[r][j];
+            const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
+            const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
+            const float dd = __fsub_rn(fabsf(__fsub_rn(sv, p.rg_mid)), p.rg_half);   // signed distance to the interval
+            nib = __funnelshift_l(__float_as_uint(dd), nib, 1);
+            unc = (unc << 1) | (fabsf(dd) <= eps ? 1u : 0u);
+          }
+          if (unc) {   // rare: pixels inside the band are redone in the oracle's exact order
+            for (int j = 0; j < 4; ++j)
+              if (unc >> j & 1u) {
+                const float* mc = M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX;
+                const float v = *mc;
+                const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur1_exact<HS>(mc, p))));
+                nib = (sv >= p.rg_min && sv <= p.rg_max) ? (nib | (1u << j)) : (nib & ~(1u << j));
+              }
+          }
+          nib &= xmask;
+          uint32_t word = nib << (4 * (lane & 7));
+          word |= __shfl_xor_sync(0xffffffffu, word, 1);
+          word |= __shfl_xor_sync(0xffffffffu, word, 2);
+          word |= __shfl_xor_sync(0xffffffffu, word, 4);
+          if (p.predicate && (lane & 7) == 0 && oy < h) {
+            const int wi = (x0 >> 5) + (lane >> 3);
+            if (wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = word;
+          }
+          if (p.median && oy < h) {
+            const size_t rowoff = ((size_t)slice * h + oy) * w;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (ox + j < w) p.median[rowoff + ox + j] = cv[r][j];
+          }
+        }
+      }
+      mbar_arrive(&bar_mempty[b]);
+      WS_STAMP(t == 0, 6);    // border composition, sharpen, predicate
+    }
+  }
+  __syncthreads();
+  // the last CTA to leave resets the work counter for the next launch that uses it
+  if (p.sched && tid == 0) {
+    __threadfence();
+    if (atomicAdd(&p.sched[1], 1u) == gridDim.x - 1) {
+      p.sched[0] = 0u; p.sched[1] = 0u; __threadfence();
+#ifdef NM03_TUNE_STAMPS
+      if (p.n >= 400)
+        printf("k1_ws cycles summed over CTAs: loader wait-release %llu wait-tma %llu work %llu | median wait %llu work %llu | sharpen wait %llu work %llu\n",
+               g_ws_stamps[0], g_ws_stamps[1], g_ws_stamps[2], g_ws_stamps[3], g_ws_stamps[4], g_ws_stamps[5], g_ws_stamps[6]);
+#endif
+    }
+  }
+}
+
+template <int K, int HS, int MODE>
+static cudaError_t launch_k1_ws(const PreParams& p, const CUtensorMap& map, cudaStream_t s) {
+  static int sm_count[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && sm_count[dev] == 0) cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+  const int slots = (dev >= 0 && dev < 64 && sm_count[dev] > 0) ? sm_count[dev] : 148;
+  const int total = p.n * p.tiles_x * p.tiles_y;
+  k1_ws<K, HS, MODE><<<total < slots ? total : slots, WS_THREADS, ws_smem_bytes<K>(), s>>>(p, map);
+  return cudaGetLastError();
+}
+
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -673,6 +1120,9 @@ static cudaError_t launch_k1m(const PreParams& p0, cudaStream_t s) {
   CUtensorMap map;
   memset(&map, 0, sizeof(map));
   p.use_tma = p0.use_tma && make_tmap(p, R, &map);
+  if constexpr (MODE != K1_EXACT) {
+    if (g_k1_ws && p.use_tma && !p.border_zero) return launch_k1_ws<K, HS, MODE>(p, map, s);
+  }
   // persistent grid: at most one CTA per resident slot (K1_MIN_CTAS per SM), each loops over work items
   static int sm_count[64] = {0};
   int dev = 0;
@@ -695,6 +1145,12 @@ static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
+  {
+    cudaError_t e2 = cudaFuncSetAttribute(k1_ws<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem_bytes<K>());
+    if (e2 == cudaSuccess && HS > 2)
+      e2 = cudaFuncSetAttribute(k1_ws<K, HS, (HS > 2 ? K1_FAST_HE2 : K1_FAST_FULL)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem_bytes<K>());
+    if (e2 != cudaSuccess) return e2;
+  }
   const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 128);
   cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
