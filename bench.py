@@ -341,6 +341,10 @@ def main():
 
     serial_ms = timed_region(serial_steps, 1)
     k1_ms, k23_ms, calls = ctx.profile_read()
+    # and once more as in the headline region (all streams), for the record: there the events around a kernel also span
+    # whatever the neighbouring steps run at the same time
+    timed_region(serial_steps, n_streams)
+    k1_ov_ms, k23_ov_ms, calls_ov = ctx.profile_read()
     ctx.profile_enable(False)
     step = real_step
 
@@ -438,6 +442,8 @@ def main():
                                         f"{PROFILE_EVERY}th step (the headline region runs {n_streams} streams, where "
                                         "kernels of neighbouring steps overlap)",
                          "single_stream_ms_per_step": serial_ms / serial_steps,
+                         "avg_launch_ms_with_all_streams": k1_ov_ms / max(calls_ov, 1),
+                         "k23_avg_launch_ms_with_all_streams": k23_ov_ms / max(calls_ov, 1),
                          "share_of_step": (k1_ms / max(calls, 1)) / (serial_ms / serial_steps) if serial_ms > 0 else None,
                          "sampled_launches": calls,
                          "k23_avg_launch_ms": k23_ms / max(calls, 1),
