@@ -93,20 +93,44 @@ class Image {
   Image(int w, int h, DataType t, int channels = 1) : w_(w), h_(h), c_(channels), type_(t) {
     bytes_.resize((size_t)w * h * channels * elemSize(t));
   }
+  // a view of pixels owned by someone else (the batch driver's pinned staging buffers): no copy, caller keeps them alive
+  static std::shared_ptr<Image> view(const void* pixels, int w, int h, DataType t) {
+    std::shared_ptr<Image> im(new Image(w, h, t, 1, nullptr));
+    im->ext_ = pixels;
+    return im;
+  }
+  // an RGB canvas all of whose pixels are grey, kept as ONE channel until somebody asks for the interleaved bytes
+  static std::shared_ptr<Image> greyCanvas(int w, int h, std::vector<uint8_t> plane) {
+    std::shared_ptr<Image> im(new Image(w, h, TYPE_UINT8, 3, nullptr));
+    im->grey_ = std::move(plane);
+    return im;
+  }
   int getWidth() const { return w_; }
   int getHeight() const { return h_; }
   int getNrOfChannels() const { return c_; }
   DataType getDataType() const { return type_; }
-  void* data() { return bytes_.data(); }
-  const void* data() const { return bytes_.data(); }
-  template <class T> T* as() { return reinterpret_cast<T*>(bytes_.data()); }
-  template <class T> const T* as() const { return reinterpret_cast<const T*>(bytes_.data()); }
+  void* data() { return const_cast<void*>(bytes()); }
+  const void* data() const { return bytes(); }
+  template <class T> T* as() { return reinterpret_cast<T*>(const_cast<void*>(bytes())); }
+  template <class T> const T* as() const { return reinterpret_cast<const T*>(bytes()); }
   static size_t elemSize(DataType t) { return t == TYPE_FLOAT ? 4 : (t == TYPE_UINT8 || t == TYPE_INT8) ? 1 : 2; }
-  bool grey3 = false;   // hint set by RenderToImage: a 3-channel canvas whose channels are known to be equal
+  // the single-channel form of a grey canvas (null for any other image); the JPEG writer takes it as it is
+  const uint8_t* greyPlane() const { return grey_.empty() ? nullptr : grey_.data(); }
  private:
+  Image(int w, int h, DataType t, int channels, std::nullptr_t) : w_(w), h_(h), c_(channels), type_(t) {}
+  const void* bytes() const {
+    if (ext_) return ext_;
+    if (bytes_.empty() && !grey_.empty()) {   // first access to the interleaved form of a grey canvas
+      bytes_.resize(grey_.size() * 3);
+      for (size_t i = 0; i < grey_.size(); ++i) bytes_[3 * i] = bytes_[3 * i + 1] = bytes_[3 * i + 2] = grey_[i];
+    }
+    return bytes_.data();
+  }
   int w_, h_, c_;
   DataType type_;
-  std::vector<uint8_t> bytes_;
+  mutable std::vector<uint8_t> bytes_;
+  std::vector<uint8_t> grey_;
+  const void* ext_ = nullptr;
 };
 using Segmentation = Image;
 
@@ -440,8 +464,9 @@ inline void Morphology::evaluate() {
 // ---- rendering + export (CPU restatement of FAST's GL renderers; host side, e2e figure only) ------
 class Renderer : public ProcessObject {
  public:
-  // paint this renderer's input into an RGB canvas (aspect-fit, centred)
-  virtual void paint(uint8_t* rgb, int cw, int ch) = 0;
+  // paint this renderer's input into a canvas (aspect-fit, centred): stride 3 = interleaved RGB, stride 1 = one grey
+  // channel (only asked of renderers whose paintsGrey() is true)
+  virtual void paint(uint8_t* rgb, int stride, int cw, int ch) = 0;
   virtual bool paintsGrey() const { return false; }   // true: only ever writes r == g == b
  protected:
   Renderer() : ProcessObject(RENDERER) {}
@@ -458,7 +483,7 @@ class ImageRenderer : public Renderer {
   std::shared_ptr<ImageRenderer> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return me(); }
   std::shared_ptr<ImageRenderer> addInputData(std::shared_ptr<Image> d) { connectData(std::move(d)); return me(); }
   bool paintsGrey() const override { return true; }
-  void paint(uint8_t* rgb, int cw, int ch) override {
+  void paint(uint8_t* rgb, int stride, int cw, int ch) override {
     auto img = inputImage();
     const int w = img->getWidth(), h = img->getHeight();
     const size_t n = (size_t)w * h;
@@ -498,6 +523,10 @@ class ImageRenderer : public Renderer {
         lut[k] = (uint8_t)(int)(std::min(255.0f, std::max(0.0f, g)) + 0.5f);
       }
       size_t i = 0;
+      if (stride == 1) {
+        for (; i < n; ++i) rgb[i] = lut[(sg ? (int)ss[i] : (int)su[i]) - lo_i];
+        return;
+      }
       for (; i + 4 <= n; i += 4) {   // four pixels = twelve canvas bytes, written as three words
         uint32_t g[4];
         for (int k = 0; k < 4; ++k) g[k] = lut[(sg ? (int)ss[i + k] : (int)su[i + k]) - lo_i];
@@ -522,7 +551,7 @@ class ImageRenderer : public Renderer {
     const float inv = hi > lo ? 255.0f / (hi - lo) : 0.0f;
     auto grey = [&](float x) { const float g = (x - lo) * inv; return (uint8_t)(int)(std::min(255.0f, std::max(0.0f, g)) + 0.5f); };
     if (w == cw && h == ch) {  // canvas and image have the same size: the fit is the identity
-      for (size_t i = 0; i < n; ++i) { const uint8_t g = grey(v[i]); rgb[3 * i] = rgb[3 * i + 1] = rgb[3 * i + 2] = g; }
+      for (size_t i = 0; i < n; ++i) { const uint8_t g = grey(v[i]); for (int k = 0; k < stride; ++k) rgb[stride * i + k] = g; }
       return;
     }
     const Fit f = fit(w, h, cw, ch);
@@ -540,8 +569,8 @@ class ImageRenderer : public Renderer {
         const float top = v[(size_t)y0 * w + x0] * (1 - ax) + v[(size_t)y0 * w + x1] * ax;
         const float bot = v[(size_t)y1 * w + x0] * (1 - ax) + v[(size_t)y1 * w + x1] * ax;
         const uint8_t g = grey(top * (1 - ay) + bot * ay);
-        uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
-        px[0] = px[1] = px[2] = g;
+        uint8_t* px = rgb + ((size_t)cy * cw + cx) * stride;
+        for (int k = 0; k < stride; ++k) px[k] = g;
       }
     }
   }
@@ -558,7 +587,7 @@ class SegmentationRenderer : public Renderer {
   }
   std::shared_ptr<SegmentationRenderer> connect(std::shared_ptr<ProcessObject> p) { connectParent(std::move(p)); return me(); }
   std::shared_ptr<SegmentationRenderer> addInputData(std::shared_ptr<Image> d) { connectData(std::move(d)); return me(); }
-  void paint(uint8_t* rgb, int cw, int ch) override {
+  void paint(uint8_t* rgb, int stride, int cw, int ch) override {
     auto img = inputImage();
     if (img->getDataType() != TYPE_UINT8) throw Exception("SegmentationRenderer needs a uint8 label image");
     const int w = img->getWidth(), h = img->getHeight();
@@ -617,9 +646,9 @@ class SegmentationRenderer : public Renderer {
         const Color* col = table[l];
         if (!col) continue;
         const float op = is_border(x, y, l) ? borderOpacity_ : opacity_;
-        uint8_t* px = rgb + ((size_t)cy * cw + cx) * 3;
+        uint8_t* px = rgb + ((size_t)cy * cw + cx) * stride;
         const float c[3] = {col->r, col->g, col->b};
-        for (int k = 0; k < 3; ++k) px[k] = (uint8_t)(int)(px[k] * (1 - op) + 255.0f * c[k] * op + 0.5f);
+        for (int k = 0; k < stride; ++k) px[k] = (uint8_t)(int)(px[k] * (1 - op) + 255.0f * c[k] * op + 0.5f);
       }
     }
   }
@@ -645,14 +674,21 @@ class RenderToImage : public ProcessObject {
   void update() override { evaluate(); }
  protected:
   void evaluate() override {
+    const uint8_t bg[3] = {(uint8_t)std::lround(bg_.r * 255), (uint8_t)std::lround(bg_.g * 255), (uint8_t)std::lround(bg_.b * 255)};
+    bool grey = bg[0] == bg[1] && bg[1] == bg[2];
+    for (auto& r : renderers_) grey = grey && r->paintsGrey();
+    if (grey) {
+      // every layer is grey (the reference's two exports are): one channel is painted, and the interleaved RGB bytes
+      // are only produced if somebody reads them (the JPEG writer takes the single channel)
+      std::vector<uint8_t> plane((size_t)w_ * h_, bg[0]);
+      for (auto& r : renderers_) r->paint(plane.data(), 1, w_, h_);
+      output_ = Image::greyCanvas(w_, h_, std::move(plane));
+      return;
+    }
     auto img = std::make_shared<Image>(w_, h_, TYPE_UINT8, 3);
     uint8_t* rgb = img->as<uint8_t>();
-    const uint8_t bg[3] = {(uint8_t)std::lround(bg_.r * 255), (uint8_t)std::lround(bg_.g * 255), (uint8_t)std::lround(bg_.b * 255)};
-    if (bg[0] == bg[1] && bg[1] == bg[2]) std::memset(rgb, bg[0], (size_t)w_ * h_ * 3);
-    else for (size_t i = 0; i < (size_t)w_ * h_; ++i) { rgb[3 * i] = bg[0]; rgb[3 * i + 1] = bg[1]; rgb[3 * i + 2] = bg[2]; }
-    bool grey = bg[0] == bg[1] && bg[1] == bg[2];
-    for (auto& r : renderers_) { r->paint(rgb, w_, h_); grey = grey && r->paintsGrey(); }
-    img->grey3 = grey;
+    for (size_t i = 0; i < (size_t)w_ * h_; ++i) { rgb[3 * i] = bg[0]; rgb[3 * i + 1] = bg[1]; rgb[3 * i + 2] = bg[2]; }
+    for (auto& r : renderers_) r->paint(rgb, 3, w_, h_);
     output_ = img;
   }
  private:
@@ -670,21 +706,18 @@ class ImageFileExporter : public Typed<ImageFileExporter> {
     if (img->getDataType() != TYPE_UINT8) throw Exception("ImageFileExporter: only 8-bit images can be written as JPEG");
     const int ch = img->getNrOfChannels();
     try {
-      if (ch == 3) {  // the canvases rendered here are grey; store one component when all three agree
+      if (const uint8_t* plane = img->greyPlane()) {   // a grey canvas of RenderToImage: one component, no conversion
+        jpeg::save(file_, plane, img->getWidth(), img->getHeight(), 1);
+        return;
+      }
+      if (ch == 3) {  // any other RGB image: store one component when all three agree
         const uint8_t* p = img->as<uint8_t>();
         const size_t n = (size_t)img->getWidth() * img->getHeight();
         bool grey = true;
-        if (!img->grey3) for (size_t i = 0; i < n && grey; ++i) grey = p[3 * i] == p[3 * i + 1] && p[3 * i] == p[3 * i + 2];
+        for (size_t i = 0; i < n && grey; ++i) grey = p[3 * i] == p[3 * i + 1] && p[3 * i] == p[3 * i + 2];
         if (grey) {
           std::vector<uint8_t> g(n);
-          size_t i = 0;
-          for (; i + 4 <= n; i += 4) {   // first channel of four pixels out of twelve bytes
-            uint32_t a, b, c;
-            std::memcpy(&a, p + 3 * i, 4); std::memcpy(&b, p + 3 * i + 4, 4); std::memcpy(&c, p + 3 * i + 8, 4);
-            const uint32_t o = (a & 0xFFu) | ((a >> 24) << 8) | (((b >> 16) & 0xFFu) << 16) | (((c >> 8) & 0xFFu) << 24);
-            std::memcpy(g.data() + i, &o, 4);
-          }
-          for (; i < n; ++i) g[i] = p[3 * i];
+          for (size_t i = 0; i < n; ++i) g[i] = p[3 * i];
           jpeg::save(file_, g.data(), img->getWidth(), img->getHeight(), 1);
           return;
         }

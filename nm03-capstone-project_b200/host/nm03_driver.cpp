@@ -159,10 +159,9 @@ struct Pinned {
 void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const uint8_t* mask, int w, int h) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
-  auto orig = std::make_shared<Image>(w, h, is_unsigned ? TYPE_UINT16 : TYPE_INT16);
-  std::memcpy(orig->data(), raw, (size_t)w * h * 2);
-  auto seg = std::make_shared<Image>(w, h, TYPE_UINT8);
-  std::memcpy(seg->data(), mask, (size_t)w * h);
+  // views of the pinned staging buffers (they outlive this call): no copies
+  auto orig = Image::view(raw, w, h, is_unsigned ? TYPE_UINT16 : TYPE_INT16);
+  auto seg = Image::view(mask, w, h, TYPE_UINT8);
   LabelColors colors;
   colors[1] = Color::White();
   auto rti = RenderToImage::create(Color::Black(), 512, 512);  // main_sequential.cpp:258
