@@ -327,6 +327,16 @@ def main():
     issue_ms_per_step = issue_s[0] * 1e3 / args.steps
     launches = ctx.kernel_launches() - launches0
 
+    # iterations-to-convergence of the region growing on this workload (outside every timed region)
+    d_it = torch.zeros(SLICES, dtype=torch.int32, device=dev)
+    o_it = nm03.Outputs()
+    o_it.dilated = d_out[0].data_ptr()
+    o_it.rg_iterations = d_it.data_ptr()
+    ctx.process_batch_device(d_in[0].data_ptr(), SLICES, W, H, params, o_it, stream.cuda_stream)
+    torch.cuda.synchronize()
+    rg_passes = {"mean": float(d_it.float().mean().item()), "max": int(d_it.max().item()),
+                 "note": "fill passes (down+up sweeps over the slice) until no pixel changes, per slice of one series"}
+
     # Per-kernel durations for the roofline: the same steps once more on ONE stream, where a kernel's CUDA-event
     # duration is its own (with two streams the events of one step also span the neighbouring step's kernels).
     # Events are recorded around each kernel on every 8th step only: an event between K1 and K23 defeats their
@@ -447,6 +457,7 @@ def main():
                          "share_of_step": (k1_ms / max(calls, 1)) / (serial_ms / serial_steps) if serial_ms > 0 else None,
                          "sampled_launches": calls,
                          "k23_avg_launch_ms": k23_ms / max(calls, 1),
+                         "region_growing_passes": rg_passes,
                          "binding_unit": alu,
                          "note": "K1 is bound by the integer min/max pipe (7x7 median), not HBM; see DESIGN.md"},
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": threads, "kind": "port",
