@@ -153,6 +153,8 @@ int order_after_last_use(Slot* s, cudaStream_t st) {
 
 // Is a batch that was queued through another slot, on another stream, still running on this GPU?
 bool others_in_flight(Worker* wk, const Slot* mine, cudaStream_t st) {
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;   // event queries are not allowed while a stream is being captured
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) { (void)cudaGetLastError(); return false; }
   for (auto& o : wk->slots) {
     if (&o == mine || !o.used.load(std::memory_order_relaxed) || o.last_stream.load(std::memory_order_relaxed) == st) continue;
     if (cudaEventQuery(o.done) == cudaErrorNotReady) {
