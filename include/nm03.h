@@ -111,8 +111,8 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
 
 /* Same, but every buffer is already in the memory of GPU `gpu`; work is queued on `stream`
  * (a cudaStream_t passed as void*, NULL = the worker's own stream) and the call does not wait.
- * The scratch between the two kernels belongs to one of 4 slots per GPU; a calling stream keeps the
- * slot it used last, so a caller that rotates its batches over up to 4 streams gets them overlapped on
+ * The scratch between the two kernels belongs to one of 8 slots per GPU; a calling stream keeps the
+ * slot it used last, so a caller that rotates its batches over up to 8 streams gets them overlapped on
  * the GPU (the fill kernel of one batch under the median kernel of the next); with more streams
  * than slots a slot changes hands in stream order (event wait), never concurrently. */
 int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int n, int w, int h,

@@ -36,7 +36,8 @@ int fail(int code, const char* fmt, ...) {
     if (e_ != cudaSuccess) return fail(NM03_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
   } while (0)
 
-constexpr int kSlots = 4;
+constexpr int kSlots = 8;          // stream slots per GPU
+constexpr int kChunksPerCall = 4;  // a host-buffer batch is pipelined over this many of them
 
 const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
 const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); return e && e[0] == '1'; }();
@@ -837,7 +838,7 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
   const size_t npx = (size_t)w * h;
   // Chunks of the batch are pipelined over the stream slots so that the H2D copy of one chunk, the
   // kernels of another and the D2H copy of a third overlap.
-  int chunk = (n + kSlots - 1) / kSlots;
+  int chunk = (n + kChunksPerCall - 1) / kChunksPerCall;
   if (chunk < 4) chunk = 4;
   std::vector<Slot*> used;
   int result = NM03_OK;
@@ -893,8 +894,8 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
       e = cudaMemcpyAsync(out->rg_iterations + start, so + o_it, (size_t)cnt * 4, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
     if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e)); break; }
-    // keep at most kSlots chunks in flight: the oldest slot is drained and handed back
-    if ((int)used.size() == kSlots) {
+    // keep at most kChunksPerCall chunks in flight: the oldest slot is drained and handed back
+    if ((int)used.size() == kChunksPerCall) {
       Slot* old = used.front();
       used.erase(used.begin());
       cudaStreamSynchronize(old->stream);

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 W = H = 512
 
 
-@pytest.mark.parametrize("n_streams", [2, 3, 6])   # 6 > the library's 4 slots: slots change hands between streams
+@pytest.mark.parametrize("n_streams", [2, 3, 10])   # 10 > the library's 8 slots: slots change hands between streams
 def test_interleaved_streams_match_oracle_and_single_stream(lib, n_streams):
     import torch
     dev = torch.device("cuda", 0)
