@@ -282,6 +282,7 @@ def main():
     # flight): the library keeps a scratch slot per calling stream, so the latency-bound fill/morphology kernel of
     # one series runs under the ALU-bound K1 of the next.  NM03_BENCH_STREAMS=1 gives the single-stream figure.
     n_streams = max(1, min(4, int(os.environ.get("NM03_BENCH_STREAMS", "4"))))
+    args.warmup = max(args.warmup, n_streams)   # every stream (and its scratch slot in the library) is warm before the clock starts
     streams = [torch.cuda.Stream(device=dev) for _ in range(n_streams)]
     stream = streams[0]
     d_out = torch.empty((max(2, n_streams), SLICES, H, W), dtype=torch.uint8, device=dev)   # one per stream in flight
