@@ -382,7 +382,7 @@ def main():
         for t in ths:
             t.join()
 
-    run_feeders(4)
+    run_feeders(8 * n_feed)   # warm-up: every stream slot of the library has sized its staging buffers before the clock starts
     barrier()
     t0 = time.perf_counter()
     run_feeders(e2e_steps)
