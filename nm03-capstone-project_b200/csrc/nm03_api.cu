@@ -37,7 +37,8 @@ int fail(int code, const char* fmt, ...) {
   } while (0)
 
 constexpr int kSlots = 8;          // stream slots per GPU
-constexpr int kChunksPerCall = 4;  // a host-buffer batch is pipelined over this many of them
+const bool g_chunks_forced = getenv("NM03_CHUNKS") != nullptr;
+const int kChunksPerCall = [] { const char* e = getenv("NM03_CHUNKS"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 8 ? v : 4; }();  // a host-buffer batch is pipelined over this many of them (NM03_CHUNKS: tuning)
 
 const bool g_no_tma = [] { const char* e = getenv("NM03_NO_TMA"); return e && e[0] == '1'; }();  // A/B measurements
 const bool g_no_tile_order = [] { const char* e = getenv("NM03_NO_TILE_ORDER"); return e && e[0] == '1'; }();
@@ -83,6 +84,7 @@ struct ProfRec {
 struct Worker {
   int device = 0;
   Slot slots[kSlots];
+  std::atomic<int> host_calls{0};   // nm03_process_batch calls in flight on this GPU
   std::mutex mu;
   std::condition_variable cv;
   std::atomic<long long> launches{0};
@@ -838,7 +840,18 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
   const size_t npx = (size_t)w * h;
   // Chunks of the batch are pipelined over the stream slots so that the H2D copy of one chunk, the
   // kernels of another and the D2H copy of a third overlap.
-  int chunk = (n + kChunksPerCall - 1) / kChunksPerCall;
+  // A lone caller gets its batch pipelined in chunks; when other host-buffer batches are in flight on this GPU they
+  // already overlap each other's copies and kernels, and whole batches keep the H2D engine busier than interleaved
+  // chunks do (3 feeder threads, 24 slices of 512x512: 96 000 slices/s unchunked, 84 000 in 4 chunks; one thread:
+  // 63 500 in 4 chunks).
+  struct InFlight {
+    std::atomic<int>& c;
+    int before;
+    explicit InFlight(std::atomic<int>& x) : c(x), before(x.fetch_add(1)) {}
+    ~InFlight() { c.fetch_sub(1); }
+  } in_flight(wk->host_calls);
+  const int n_chunks = (in_flight.before > 0 && !g_chunks_forced) ? 1 : kChunksPerCall;
+  int chunk = (n + n_chunks - 1) / n_chunks;
   if (chunk < 4) chunk = 4;
   std::vector<Slot*> used;
   int result = NM03_OK;
@@ -862,8 +875,12 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
     const size_t o_sh = out_bytes; if (out->sharpened) out_bytes += cnt * npx * 4;
     const size_t o_med = out_bytes; if (out->median) out_bytes += cnt * npx * 4;
     const size_t o_it = out_bytes; if (out->rg_iterations) out_bytes += (size_t)cnt * 4;
-    rc = ensure(s, &s->stage_in, &s->stage_in_bytes, cnt * npx * 2);
-    if (!rc) rc = ensure(s, &s->stage_out, &s->stage_out_bytes, out_bytes ? out_bytes : 16);
+    // staging is sized for the whole batch even when this call works in chunks: the next batch of this shape may
+    // come unchunked (see above), and growing a buffer then would put a cudaFree/cudaMalloc in its path
+    const size_t per_slice = npx * ((out->dilated ? 1 : 0) + (out->eroded ? 1 : 0) + (out->rg_mask ? 1 : 0) +
+                                    (out->sharpened ? 4 : 0) + (out->median ? 4 : 0)) + (out->rg_iterations ? 4 : 0);
+    rc = ensure(s, &s->stage_in, &s->stage_in_bytes, (size_t)n * npx * 2);
+    if (!rc) rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n * per_slice + 32));
     if (rc) { result = rc; break; }
     cudaStream_t st = s->stream;
     cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
@@ -895,7 +912,7 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
     if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
     if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e)); break; }
     // keep at most kChunksPerCall chunks in flight: the oldest slot is drained and handed back
-    if ((int)used.size() == kChunksPerCall) {
+    if ((int)used.size() == n_chunks) {
       Slot* old = used.front();
       used.erase(used.begin());
       cudaStreamSynchronize(old->stream);
