@@ -205,12 +205,16 @@ def driver_io_figure():
                                   stdout=subprocess.DEVNULL)
             out = {}
             for name, extra in (("dicom_to_mask", ["--no-export"]), ("dicom_to_jpeg", [])):
-                r = subprocess.run([drv, "--data", td + "/d", "--out", td + "/o", "--gpus", "0"] + extra, capture_output=True,
-                                   text=True, timeout=300)
-                rep = json.loads(r.stdout.strip().splitlines()[-1])
+                rep = None
+                for _ in range(2):   # a 480-slice run lasts 20-60 ms and the first process pays for cold files: best of two
+                    r = subprocess.run([drv, "--data", td + "/d", "--out", td + "/o", "--gpus", "0"] + extra, capture_output=True,
+                                       text=True, timeout=300)
+                    one = json.loads(r.stdout.strip().splitlines()[-1])
+                    if rep is None or one["slices_per_sec"] > rep["slices_per_sec"]:
+                        rep = one
                 out[name + "_slices_per_sec"] = rep["slices_per_sec"]
                 out[name + "_startup_seconds"] = rep.get("startup_seconds")   # context, pinned ring, kernel load: not in the rate
-            out["sample"] = f"20 patients x {SLICES} slices {W}x{H} (BASELINE configs[2]), DICOM files in a memory-backed temp dir, timed after context start-up"
+            out["sample"] = f"20 patients x {SLICES} slices {W}x{H} (BASELINE configs[2]), DICOM files in a memory-backed temp dir, timed after context start-up, best of two runs"
             return out
     except Exception as e:  # informational only
         return {"error": str(e)[:200]}
