@@ -287,7 +287,7 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   for (int i = 0; i < m * m; ++i) k.mask[i] /= sum;
   for (int i = m * m; i < 81; ++i) k.mask[i] = 0.0f;
   for (int i = 0; i < 9; ++i) k.gx[i] = 0.0f;
-  k.ea = k.eb = k.ec = 0.0f;
+  k.ea = k.eb = k.ec = k.eps_max = 0.0f;
   return NM03_OK;
 }
 
@@ -355,6 +355,10 @@ int fill_fast(nm03::PreParams& k, const nm03_params* p, int sharpen_half) {
     k.ea = (float)(ea2 * 1.02) + 1e-12f;
     k.eb = (float)(eb2 * 1.02) + 1e-12f;
     k.ec = (float)(ec2 * 1.02) + 1e-12f;
+    // widest band of any pixel: |v| <= vmax and |blur_a| <= (sum |gx|)^2 * vmax (inflated for the rounding of the FMAs)
+    double gsum = 0.0;
+    for (int x = -he; x <= he; ++x) gsum += std::fabs((double)k.gx[x + nm03::K1_HS_MAX]);
+    k.eps_max = (float)(((double)k.ea * gsum * gsum * 1.0001 + (double)k.eb) * vmax * 1.0001 + (double)k.ec) + 1e-12f;
     best_mode = (he < hs) ? nm03::K1_FAST_HE2 : nm03::K1_FAST_FULL;
     break;
   }

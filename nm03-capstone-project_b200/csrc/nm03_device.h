@@ -57,6 +57,7 @@ struct PreParams {
   // than eps to a threshold are recomputed in the oracle's exact order.
   float gx[9];
   float ea, eb, ec;
+  float eps_max;                 // upper bound of eps over every |blur|, |v| these parameters can produce
   float rg_mid, rg_half;         // fast predicate: inside [rg_min, rg_max]  <=>  |s - rg_mid| - rg_half <= 0 (up to the band)
 };
 

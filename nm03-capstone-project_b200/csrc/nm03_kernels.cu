@@ -162,6 +162,22 @@ __device__ __noinline__ float blur1_exact(const float* __restrict__ Mc, const Pr
   return acc;
 }
 
+// Separable blur of ONE pixel with exactly the operations (and order) of the straight-line fast path of phase C:
+// per row a chain of FMAs over the taps from 0.0f, then a chain over the rows.  Used off the hot path to redo the
+// band test of a pixel with its own error bound.
+template <int HE>
+__device__ __noinline__ float blur1_fast(const float* __restrict__ Mc, const PreParams& p) {
+  float blur = 0.0f;
+#pragma unroll 1
+  for (int t = -HE; t <= HE; ++t) {
+    float a = 0.0f;
+#pragma unroll
+    for (int u = -HE; u <= HE; ++u) a = __fmaf_rn(p.gx[u + K1_HS_MAX], Mc[t * K1_MW + u], a);
+    blur = __fmaf_rn(p.gx[t + K1_HS_MAX], a, blur);
+  }
+  return blur;
+}
+
 // ---- TMA helpers (cp.async.bulk.tensor + mbarrier, PTX ISA 8.x; SASS: UTMALDG / SYNCS) ------------
 __device__ __forceinline__ uint32_t smem_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -207,7 +223,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   static_assert(K1_MW % RUN == 0 && RUN % 2 == 0, "median tile width must be a multiple of the (even) run length");
 
   extern __shared__ __align__(16) uint32_t smem_raw[];
-  uint32_t* smem = reinterpret_cast<uint32_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);  // TMA dst: 128 B
+  // TMA destination: 128-byte aligned.  The padding is added as an element offset to the __shared__ array, so the
+  // compiler keeps the shared address space (LDS/STS with 32-bit addresses); rounding the pointer through uintptr_t
+  // turned every tile access into a generic LD.E/ST.E with 64-bit address arithmetic.
+  uint32_t* smem = smem_raw + (((128u - (smem_u32(smem_raw) & 127u)) & 127u) >> 2);
   uint32_t* P = smem;                                         // [PR][K1_PWS] packed keys (row q | row q+36 <<16)
   float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median)
 
@@ -324,13 +343,19 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       // rows gy0+q and gy0+q+36
       const int cl = p.border_zero ? K1_PWS : max(0, -gx0), cr = p.border_zero ? K1_PWS : min(K1_PWS, w - gx0);
       const int warp = tid >> 5, ln = tid & 31;
-      for (int q = warp; q < PR; q += K1_THREADS / 32) {
-        const int gya = gy0 + q, gyb = gya + K1_MHP;
-        if (gya < 0 || gyb >= h || gya >= h || gyb < 0 || p.border_zero) {
+      auto row_outside = [&](int q) { const int gya = gy0 + q, gyb = gya + K1_MHP; return gya < 0 || gyb >= h || gya >= h || gyb < 0 || p.border_zero; };
+      // rows with a half above or below the image: the whole row, one warp per row
+      for (int q = warp; q < PR; q += K1_THREADS / 32)
+        if (row_outside(q))
           for (int col = ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
-        } else {
-          for (int col = ln; col < cl; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
-          for (int col = cr + ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+      // the other rows: only the few columns left / right of the image, eight lanes per row (a side strip is 7-9 columns
+      // wide for whole tiles, so a full warp per row would leave three quarters of its lanes idle)
+      if (cl > 0 || cr < K1_PWS) {
+        const int grp = tid >> 3, gl = tid & 7;
+        for (int q = grp; q < PR; q += K1_THREADS / 8) {
+          if (row_outside(q)) continue;
+          for (int col = gl; col < cl; col += 8) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          for (int col = cr + gl; col < K1_PWS; col += 8) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
         }
       }
     }
@@ -505,13 +530,16 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       if (!p.border_zero && rb > rt && cr > cl) val = M[cy * K1_MW + clampi(mx, cl, cr - 1)];  // reads in-image cells only
       M[my * K1_MW + mx] = val;                                                                 // writes outside cells only
     };
-    for (int my = warp; my < K1_MH; my += K1_THREADS / 32) {
-      const int cy = clampi(my, rt, rb - 1);
-      if (my < rt || my >= rb) {
-        for (int mx = ln; mx < K1_MW; mx += 32) fill(my, mx, cy);
-      } else {
-        for (int mx = ln; mx < cl; mx += 32) fill(my, mx, cy);
-        for (int mx = cr + ln; mx < K1_MW; mx += 32) fill(my, mx, cy);
+    // rows above / below the image: whole rows, one warp per row; the other rows: the few columns beside the image,
+    // eight lanes per row (the strip is at most K1_HS_MAX columns wide for whole tiles)
+    for (int my = warp; my < K1_MH; my += K1_THREADS / 32)
+      if (my < rt || my >= rb)
+        for (int mx = ln; mx < K1_MW; mx += 32) fill(my, mx, clampi(my, rt, rb - 1));
+    if (cl > 0 || cr < K1_MW) {
+      const int grp = tid >> 3, gl = tid & 7;
+      for (int my = rt + grp; my < rb; my += K1_THREADS / 8) {
+        for (int mx = gl; mx < cl; mx += 8) fill(my, mx, my);
+        for (int mx = cr + gl; mx < K1_MW; mx += 8) fill(my, mx, my);
       }
     }
     __syncthreads();
@@ -609,19 +637,26 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
           for (int t = 0; t < NT; ++t) blur = __fmaf_rn(p.gx[t + (K1_HS_MAX - HE)], hsum[r + t][j], blur);
           const float v = cv[r][j];
           const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
-          const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
-          // signed distance to the interval: negative inside; decided by its sign unless it lies in the band
+          // signed distance to the interval: negative inside; decided by its sign unless it lies in the band.  The
+          // straight-line code tests against the widest band any pixel can have (eps_max >= eps for every |blur|, |v|);
+          // the pixel's own band is only worked out for the few that pass this test.
           const float d = __fsub_rn(fabsf(__fsub_rn(sv, p.rg_mid)), p.rg_half);
           nib = __funnelshift_l(__float_as_uint(d), nib, 1);
-          unc = (unc << 1) | (fabsf(d) <= eps ? 1u : 0u);
+          unc = (unc << 1) | (fabsf(d) <= p.eps_max ? 1u : 0u);
         }
-        if (unc) {   // rare: pixels inside the band are redone in the oracle's exact order, off the straight-line path
+        if (unc) {   // rare: pixels inside their band are redone in the oracle's exact order, off the straight-line path
           for (int j = 0; j < 4; ++j)
             if (unc >> j & 1u) {
               const float* mc = M + (oyl0 + r + K1_HS_MAX) * K1_MW + 4 * xq + j + K1_HS_MAX;
               const float v = *mc;
-              const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur1_exact<HS>(mc, p))));
-              nib = (sv >= p.rg_min && sv <= p.rg_max) ? (nib | (1u << j)) : (nib & ~(1u << j));
+              const float blur = blur1_fast<HE>(mc, p);   // bit-identical to the value computed above
+              const float svf = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur)));
+              const float eps = __fmaf_rn(p.ea, fabsf(blur), __fmaf_rn(p.eb, fabsf(v), p.ec));
+              const float d = __fsub_rn(fabsf(__fsub_rn(svf, p.rg_mid)), p.rg_half);
+              if (fabsf(d) <= eps) {
+                const float sv = __fadd_rn(v, __fmul_rn(p.gain, __fsub_rn(v, blur1_exact<HS>(mc, p))));
+                nib = (sv >= p.rg_min && sv <= p.rg_max) ? (nib | (1u << j)) : (nib & ~(1u << j));
+              }
             }
         }
         nib &= xmask;
@@ -711,7 +746,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) k1_ws(const __grid_constant__ P
   static_assert(MODE != K1_EXACT, "the warp-specialised kernel implements the fast predicate modes only");
 
   extern __shared__ __align__(16) uint32_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  uint8_t* base = reinterpret_cast<uint8_t*>(smem_raw + (((128u - (smem_u32(smem_raw) & 127u)) & 127u) >> 2));   // keeps the shared address space
   constexpr size_t T_BYTES = (((size_t)RH * K1_PWS * 2 + 127) / 128) * 128, P_BYTES = (size_t)PR * K1_PWS * 4, M_BYTES = (size_t)K1_MH * K1_MW * 4;
   constexpr size_t W_BYTES = (size_t)((NITEMS * 2 + 15) / 16) * 16;
   static_assert(T_BYTES % 128 == 0 && P_BYTES % 16 == 0 && M_BYTES % 16 == 0, "tile buffers must keep their alignment");

@@ -162,6 +162,22 @@ def o_pipeline(raw, p=None, want=("median", "sharpened", "rg_mask", "dilated", "
     return rc, res
 
 
+def o_batch_omp(slices, p=None, threads=0):
+    """The oracle in the reference's OpenMP batch-of-25 structure (main_parallel.cpp:330-347) over a whole
+    (n, h, w) series; returns the (n, h, w) uint8 dilated masks.  threads=0 = every core of the box."""
+    slices = np.ascontiguousarray(slices)
+    n, h, w = slices.shape
+    p = p or oparams()
+    if slices.dtype == np.uint16:
+        p.input_unsigned = 1
+    if threads <= 0:
+        threads = len(os.sched_getaffinity(0))
+    out = np.empty((n, h, w), np.uint8)
+    ok = oracle().nm03o_run_batch_omp(_ptr(slices), n, w, h, C.byref(p), 25, threads, _ptr(out))
+    assert ok == n, f"oracle processed {ok} of {n} slices"
+    return out
+
+
 def phantom(w, h, patient=0, slice_idx=0, kind="default", dtype=np.int16):
     """Deterministic T1+C-like phantom: 12-bit range, background N(40,15)>=0, head
     ellipse (axes .42w,.48h) tissue N(1000,60), skull ring 600, 1-3 enhancing blobs N(1600,120) near

@@ -6,27 +6,28 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 24
+W = H = int(sys.argv[2]) if len(sys.argv) > 2 else 512
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 100
 nm03 = importlib.import_module("nm03-capstone-project_b200")
 dev = torch.device("cuda", 0)
 ctx = nm03.Context([0])
-d_in = bench.torch_series(torch, 24, dev, 1234)          # 24 series x 24 slices
-flat = d_in.reshape(-1, bench.H, bench.W)
+d_in = bench.torch_series(torch, 24, dev, 1234, dict(bench.CONFIGS['c2'], w=W, h=H))          # 24 series x 24 slices
+flat = d_in.reshape(-1, H, W)
 n_batches = flat.shape[0] // n
-d_out = torch.empty((n, bench.H, bench.W), dtype=torch.uint8, device=dev)
+d_out = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
 o = nm03.Outputs(); o.dilated = d_out.data_ptr()
 it = torch.zeros(n, dtype=torch.int32, device=dev); o.rg_iterations = it.data_ptr()
 params = nm03.default_params()
 st = torch.cuda.Stream(device=dev)
 for i in range(5):
-    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, bench.W, bench.H, params, o, st.cuda_stream)
+    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, W, H, params, o, st.cuda_stream)
 torch.cuda.synchronize()
 prof = os.environ.get('K_TIME_NOPROF') != '1'
 ctx.profile_enable(prof)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record(st)
 for i in range(steps):
-    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, bench.W, bench.H, params, o, st.cuda_stream)
+    ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, W, H, params, o, st.cuda_stream)
 e1.record(st)
 torch.cuda.synchronize()
 k1, k23, calls = ctx.profile_read() if prof else (0.0, 0.0, 1)
