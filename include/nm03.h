@@ -39,7 +39,8 @@ typedef enum nm03_status {
   NM03_ERR_TOO_LARGE = -7,     /* batch or slice exceeds a fixed capacity (built-in scratch of the _noalloc entry point; rows too wide for the band fallback) */
   NM03_ERR_CUDA = -8,          /* CUDA runtime error (message has the detail) */
   NM03_ERR_NO_DEVICE = -9,
-  NM03_ERR_NOMEM = -10
+  NM03_ERR_NOMEM = -10,
+  NM03_ERR_BUSY = -11          /* nm03_process_batch_async: every stream slot of the GPU holds an unfinished ticket; wait for one first */
 } nm03_status;
 
 /* switch values for the details of FAST that cannot be verified offline */
@@ -52,7 +53,7 @@ enum { NM03_MORPH_DILATE = 0, NM03_MORPH_ERODE = 1 };
 typedef struct nm03_params {
   float norm_low, norm_high, norm_min, norm_max; /* IntensityNormalization::create(0.5f,2.5f,0.0f,10000.0f) main_sequential.cpp:195-196 */
   float clip_min, clip_max;                      /* IntensityClipping::create(0.68f,4000.0f)     main_sequential.cpp:200 */
-  int median_window;                             /* VectorMedianFilter::create(7)                main_sequential.cpp:204 */
+  int median_window;                             /* VectorMedianFilter::create(7)                main_sequential.cpp:204; any odd size 3..15 */
   float sharpen_gain, sharpen_sigma;             /* ImageSharpening::create(2.0f,0.5f,9)         main_sequential.cpp:208 */
   int sharpen_mask;
   float rg_min, rg_max;                          /* SeededRegionGrowing::create(0.74f,0.91f,..)  main_sequential.cpp:232-233 */
@@ -76,6 +77,11 @@ typedef struct nm03_outputs {
   float* sharpened;    /* sharpen output (test_pipeline.cpp:71-73) */
   float* median;       /* medianfilter output */
   int32_t* rg_iterations; /* [n] passes the flood fill needed to converge */
+  /* The final result once more, bit-packed: [n][h][ceil(w/32)] 32-bit words, bit x%32 of word x/32 of a row = pixel x
+   * (unused high bits of the last word are 0).  No counterpart in the reference (FAST images are one byte per label);
+   * it is the form the segmentation kernel holds the mask in, and it crosses the host link at 1/8 of the bytes of
+   * `dilated`.  May be requested with or without `dilated`. */
+  uint32_t* dilated_bits;
 } nm03_outputs;
 
 typedef struct nm03_ctx nm03_ctx;
@@ -104,10 +110,29 @@ int nm03_make_seeds(int w, int h, int* xy, int cap);
 /* processSingleImage() for n slices of one size, host buffers in and out (main_parallel.cpp:66-170
  * applied to a batch, main_parallel.cpp:336-343).  slices: [n][h][w] int16 (or uint16 if
  * params->input_unsigned).  seeds_xy may be NULL = the adaptive seeds of nm03_make_seeds(w,h).
- * status (optional, [n]) receives a per-slice nm03_status; a failed slice never poisons the batch
- * (the reference's catch-and-continue, main_parallel.cpp:163-167). */
+ * The call returns when every requested output is in the caller's buffers.  A lone caller gets its batch cut into a
+ * few chunks that are pipelined over the stream slots (copy in / kernels / copy out overlap); when other host-buffer
+ * calls are in flight on the same GPU the batch goes through whole, because the calls already overlap each other.
+ * status (optional, [n]): every cause of failure here is a property of the whole call (size below 100, a parameter
+ * FAST would reject, a seed outside the image, a CUDA error), so all n entries receive the call's return value.  The
+ * reference's catch-and-continue (main_parallel.cpp:163-167) therefore happens at the granularity the caller batches
+ * at: a driver that wants a bad slice not to take others with it groups slices by size, as nm03_driver does. */
 int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
                        const int* seeds_xy, int n_seeds, const nm03_outputs* out, int* status);
+
+/* The same work without waiting for it (SURVEY §8b "async variant with stream ticket"): the copies and kernels of the
+ * batch are queued on one of the GPU's 8 stream slots and the call returns a ticket; nm03_wait blocks until the
+ * outputs are in the caller's buffers, reports the result and frees the ticket (also after an error).  Input and
+ * output buffers must stay valid and untouched until then, and should be pinned (nm03_host_alloc) — with pageable
+ * memory the copies fall back to staged, partly synchronous transfers.  One host thread can keep several batches in
+ * flight this way (three saturate the host link), where the reference needs its 16 OpenMP threads
+ * (main_parallel.cpp:336-343,401) to overlap anything.  At most 8 tickets per GPU can be outstanding: with all
+ * slots taken the call returns NM03_ERR_BUSY instead of blocking (the caller may hold every ticket itself).
+ * nm03_wait may be called from any thread, once per ticket. */
+typedef struct nm03_ticket nm03_ticket;
+int nm03_process_batch_async(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
+                             const int* seeds_xy, int n_seeds, const nm03_outputs* out, nm03_ticket** ticket);
+int nm03_wait(nm03_ticket* ticket);
 
 /* Same, but every buffer is already in the memory of GPU `gpu`; work is queued on `stream`
  * (a cudaStream_t passed as void*, NULL = the worker's own stream) and the call does not wait.
@@ -184,6 +209,13 @@ long long nm03_kernel_launches(const nm03_ctx* ctx, int gpu);
  * pipeline calls since the last read, and resets the sums. */
 int nm03_profile_enable(nm03_ctx* ctx, int gpu, int on);
 int nm03_profile_read(nm03_ctx* ctx, int gpu, double* preprocess_ms, double* segment_ms, long long* calls);
+/* Work counter of the preprocess kernel, for the ALU roofline of benchmarks (no counterpart in the reference):
+ * the number of median work items (one thread computing a run of adjacent outputs with the generated min/max
+ * network) the kernel actually sorted on `gpu` since the last call — windows that take the clip-floor shortcut are
+ * not counted.  Waits for the GPU, returns the count and resets it.  nm03_median_network_ops(window) = min/max
+ * instructions one such work item executes (0 for a window without a generated network). */
+long long nm03_profile_work(nm03_ctx* ctx, int gpu);
+int nm03_median_network_ops(int median_window);
 
 #ifdef __cplusplus
 }

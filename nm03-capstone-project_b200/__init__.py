@@ -20,13 +20,14 @@ EXPORTS = [
     "nm03_make_seeds", "nm03_process_batch", "nm03_process_batch_device", "nm03_host_alloc", "nm03_host_free",
     "nm03_preprocess", "nm03_region_grow", "nm03_morphology", "nm03_kernel_launches",
     "nm03_profile_enable", "nm03_profile_read", "nm03_process_batch_device_noalloc", "nm03_device_count",
+    "nm03_process_batch_async", "nm03_wait", "nm03_profile_work", "nm03_median_network_ops",
 ]
 
 NOALLOC_MAX_PRED_WORDS = 256 * 1024  # NM03_NOALLOC_MAX_PRED_WORDS
 
 OK = 0
 ERR_INVALID, ERR_TOO_SMALL, ERR_PARAM, ERR_NO_SEEDS, ERR_SEED_OOB = -1, -2, -3, -4, -5
-ERR_UNSUPPORTED, ERR_TOO_LARGE, ERR_CUDA, ERR_NO_DEVICE, ERR_NOMEM = -6, -7, -8, -9, -10
+ERR_UNSUPPORTED, ERR_TOO_LARGE, ERR_CUDA, ERR_NO_DEVICE, ERR_NOMEM, ERR_BUSY = -6, -7, -8, -9, -10, -11
 
 
 class Params(C.Structure):
@@ -49,6 +50,7 @@ class Outputs(C.Structure):
     _fields_ = [
         ("dilated", C.c_void_p), ("eroded", C.c_void_p), ("rg_mask", C.c_void_p),
         ("sharpened", C.c_void_p), ("median", C.c_void_p), ("rg_iterations", C.c_void_p),
+        ("dilated_bits", C.c_void_p),
     ]
 
 
@@ -80,6 +82,11 @@ def lib():
         _lib.nm03_host_free.argtypes = [C.c_void_p]
         _lib.nm03_process_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                             C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        _lib.nm03_process_batch_async.argtypes = _lib.nm03_process_batch.argtypes
+        _lib.nm03_wait.argtypes = [C.c_void_p]
+        _lib.nm03_profile_work.restype = C.c_longlong
+        _lib.nm03_profile_work.argtypes = [C.c_void_p, C.c_int]
+        _lib.nm03_median_network_ops.argtypes = [C.c_int]
         _lib.nm03_process_batch_device.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                                    C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         _lib.nm03_process_batch_device_noalloc.argtypes = _lib.nm03_process_batch_device.argtypes
@@ -107,6 +114,27 @@ def default_params(**kw):
     for k, v in kw.items():
         setattr(p, k, v)
     return p
+
+
+def median_network_ops(window):
+    """min/max instructions one median work item of the preprocess kernel executes (nm03_median_network_ops)."""
+    return lib().nm03_median_network_ops(int(window))
+
+
+def _copy_params(params, dtype):
+    """A private copy of the caller's nm03_params with input_unsigned set from the array's dtype (the caller's object is
+    not touched, so it can be reused for int16 and uint16 input alike)."""
+    q = Params()
+    C.memmove(C.byref(q), C.byref(params if params is not None else default_params()), C.sizeof(Params))
+    q.input_unsigned = 1 if dtype == np.uint16 else 0
+    return q
+
+
+class Ticket:
+    """Handle of a batch queued with Context.process_batch_async; keeps the buffers alive until wait()."""
+
+    def __init__(self, handle, keep, res):
+        self._h, self._keep, self.res = handle, keep, res
 
 
 def make_seeds(w, h):
@@ -153,6 +181,13 @@ class Context:
         _check(lib().nm03_profile_read(self._h, gpu, C.byref(a), C.byref(b), C.byref(n)))
         return a.value, b.value, n.value
 
+    def profile_work(self, gpu=0):
+        """nm03_profile_work: median work items the preprocess kernel sorted since the last call (waits for the GPU)."""
+        v = lib().nm03_profile_work(self._h, gpu)
+        if v < 0:
+            raise Nm03Error(int(v), "nm03_profile_work failed")
+        return int(v)
+
     def host_alloc(self, shape, dtype):
         """numpy array backed by pinned host memory (nm03_host_alloc)."""
         nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
@@ -165,14 +200,8 @@ class Context:
         return arr
 
     # ---- whole pipeline, host buffers -------------------------------------------------------
-    def process_batch(self, slices, params=None, seeds=None, want=("dilated",), gpu=0, out=None):
-        """slices: (n, h, w) int16/uint16 array.  Returns dict of requested outputs."""
-        slices = np.ascontiguousarray(slices)
-        n, h, w = slices.shape
-        params = params or default_params()
-        if slices.dtype == np.uint16:
-            params.input_unsigned = 1
-        res = out if out is not None else {}
+    @staticmethod
+    def _host_outputs(n, h, w, want, res):
         o = Outputs()
         for name in want:
             if name not in res:
@@ -180,9 +209,20 @@ class Context:
                     res[name] = np.empty((n, h, w), np.float32)
                 elif name == "rg_iterations":
                     res[name] = np.zeros(n, np.int32)
+                elif name == "dilated_bits":
+                    res[name] = np.empty((n, h, (w + 31) // 32), np.uint32)
                 else:
                     res[name] = np.empty((n, h, w), np.uint8)
             setattr(o, name, res[name].ctypes.data)
+        return o
+
+    def process_batch(self, slices, params=None, seeds=None, want=("dilated",), gpu=0, out=None):
+        """slices: (n, h, w) int16/uint16 array.  Returns dict of requested outputs."""
+        slices = np.ascontiguousarray(slices)
+        n, h, w = slices.shape
+        params = _copy_params(params, slices.dtype)
+        res = out if out is not None else {}
+        o = self._host_outputs(n, h, w, want, res)
         status = np.zeros(n, np.int32)
         sp = None if seeds is None else np.ascontiguousarray(seeds, np.int32)
         rc = lib().nm03_process_batch(self._h, gpu, _p(slices), n, w, h, C.byref(params), _p(sp),
@@ -190,6 +230,29 @@ class Context:
         res["status"] = status
         _check(rc)
         return res
+
+    def process_batch_async(self, slices, params=None, out=None, want=("dilated",), seeds=None, gpu=0):
+        """nm03_process_batch_async: queue the batch and return a Ticket; `out` maps output names to (preferably pinned)
+        arrays that receive the results, which are valid after wait(ticket).  Raises Nm03Error(ERR_BUSY) when all
+        stream slots of the GPU hold unfinished tickets."""
+        slices = np.ascontiguousarray(slices)
+        n, h, w = slices.shape
+        params = _copy_params(params, slices.dtype)
+        res = out if out is not None else {}
+        o = self._host_outputs(n, h, w, tuple(res.keys()) if out is not None else want, res)
+        sp = None if seeds is None else np.ascontiguousarray(seeds, np.int32)
+        t = C.c_void_p()
+        _check(lib().nm03_process_batch_async(self._h, gpu, _p(slices), n, w, h, C.byref(params), _p(sp),
+                                              0 if sp is None else len(sp), C.byref(o), C.byref(t)))
+        return Ticket(t, (slices, sp, res), res)
+
+    def wait(self, ticket):
+        """nm03_wait: block until the ticket's outputs are in its buffers; returns them."""
+        h, ticket._h = ticket._h, None
+        if h is None:
+            raise ValueError("ticket was already waited for")
+        _check(lib().nm03_wait(h))
+        return ticket.res
 
     # ---- whole pipeline, device pointers ----------------------------------------------------
     def process_batch_device(self, d_slices_ptr, n, w, h, params, d_out: Outputs, stream=0, seeds=None, gpu=0):
@@ -210,9 +273,7 @@ class Context:
     def preprocess(self, raw, params=None, want=("median", "sharpened", "predicate"), gpu=0):
         raw = np.ascontiguousarray(raw)
         h, w = raw.shape
-        params = params or default_params()
-        if raw.dtype == np.uint16:
-            params.input_unsigned = 1
+        params = _copy_params(params, raw.dtype)
         med = np.empty((h, w), np.float32) if "median" in want else None
         sh = np.empty((h, w), np.float32) if "sharpened" in want else None
         pred = np.empty((h, (w + 31) // 32), np.uint32) if "predicate" in want else None
@@ -245,6 +306,12 @@ def shard_range(n_items, world, rank):
     if world <= 0 or not 0 <= rank < world:
         raise ValueError("bad world/rank")
     return (rank * n_items) // world, ((rank + 1) * n_items) // world
+
+
+def unpack_bits(bits, w):
+    """bit-packed masks (..., h, ceil(w/32)) uint32 -> (..., h, w) uint8 {0,1} (nm03_outputs.dilated_bits)."""
+    b = np.unpackbits(np.ascontiguousarray(bits).view(np.uint8).reshape(bits.shape[:-1] + (-1,)), axis=-1, bitorder="little")
+    return b[..., :w]
 
 
 def unpack_predicate(pred, w):

@@ -402,6 +402,7 @@ def emit(args):
               f"({n3 / (2.0 * run):.1f} per pixel); shared-core design, pair offset {pair_off}, "
               f"aligned blocks <= {maxlen} columns at offset {blk_off}")
         print(f"#define NM03_MEDIAN_RUNLEN_{k} {run}")
+        print(f"#define NM03_MEDIAN_OPS_{k} {n3}")
         print(f"#define NM03_MEDIAN_RUN_{k}(v, o) do {{ \\")
         in_names = [f"(v)[{c}][{r}]" for c in range(run + k - 1) for r in range(k)]
         body = net.emit_cuda(outs, in_names, [f"(o)[{i}]" for i in range(run)], indent="  ", prefix=f"m{k}_", order=ORDER)

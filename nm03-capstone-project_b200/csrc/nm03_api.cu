@@ -50,6 +50,10 @@ const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return 
 
 // NM03_FORCE_EXACT_SHARPEN=1 makes K1 evaluate the unsharp mask exactly everywhere even when only the
 // predicate is needed (A/B measurements; results are identical by construction)
+// NM03_SPIN_WAIT=1: host waits spin on the GPU's completion flag instead of sleeping until the driver wakes the
+// thread (lower wake-up latency for a lone caller, one busy core per waiting thread)
+const bool g_spin_wait = [] { const char* e = getenv("NM03_SPIN_WAIT"); return e && e[0] == '1'; }();
+
 const bool g_force_exact = [] { const char* e = getenv("NM03_FORCE_EXACT_SHARPEN"); return e && e[0] == '1'; }();
 
 struct Slot {
@@ -199,11 +203,10 @@ int check_params(const nm03_params* p, int w, int h, bool whole_pipeline) {
 }
 
 int check_preprocess(const nm03_params* p, int* sharpen_half) {
-  if (p->median_window != 3 && p->median_window != 5 && p->median_window != 7 && p->median_window != 9) {
-    if (p->median_window < 1 || (p->median_window & 1) == 0)
-      return fail(NM03_ERR_PARAM, "median window must be odd, got %d", p->median_window);
-    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (3, 5, 7, 9 are)", p->median_window);
-  }
+  if (p->median_window < 3 || (p->median_window & 1) == 0)
+    return fail(NM03_ERR_PARAM, "median window must be odd and >= 3, got %d", p->median_window);
+  if (p->median_window > 15)
+    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (odd sizes 3..15 are)", p->median_window);
   int m = p->sharpen_mask;
   if (m == 0) m = (int)std::ceil(2.0f * p->sharpen_sigma) * 2 + 1;  // FAST's default mask size
   if (m < 1 || (m & 1) == 0) return fail(NM03_ERR_PARAM, "sharpen mask size must be odd, got %d", m);
@@ -255,7 +258,7 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   // clip floor shortcut: the largest key K with f(K) == f(lowest key); f must be non-decreasing in the
   // key (both normalisation factors of one sign) and the zero-border sentinel must not be in play
   k.skip_on = 0; k.skip_key2 = 0; k.skip_val = 0.0f;
-  if (!g_no_skip && !k.border_zero && (double)k.norm_scale * (double)k.norm_range > 0.0) {
+  if (!g_no_skip && !k.border_zero && p->median_window <= 9 && (double)k.norm_scale * (double)k.norm_range > 0.0) {
     const int kmin = -32768, off = k.input_unsigned ? 32768 : 0;
     const float fmin_ = f_host((float)(kmin + off), p);
     int lo = kmin, hi = 32767;                        // invariant: f(lo) == fmin_
@@ -530,8 +533,8 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   if ((rc = order_after_last_use(s, st))) return rc;
   if ((rc = ensure_lut(wk, s, st, pre))) return rc;
   if (!s->sched) {
-    if ((rc = ensure(s, (void**)&s->sched, &s->sched_bytes, 2 * sizeof(unsigned int)))) return rc;
-    CK(cudaMemsetAsync(s->sched, 0, 2 * sizeof(unsigned int), st));
+    if ((rc = ensure(s, (void**)&s->sched, &s->sched_bytes, 4 * sizeof(unsigned int)))) return rc;
+    CK(cudaMemsetAsync(s->sched, 0, 4 * sizeof(unsigned int), st));
   }
   pre.sched = g_no_dynamic ? nullptr : s->sched;
   pre.in = d_slices;
@@ -551,6 +554,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   if (prof) CK(cudaEventRecord(rec.e[1], st));
   seg.pred = s->pred;
   seg.dilated = d_out->dilated;
+  seg.dilated_bits = d_out->dilated_bits;
   seg.eroded = (p->erode_size > 0) ? d_out->eroded : nullptr;
   seg.rg_mask = d_out->rg_mask;
   seg.iterations = d_out->rg_iterations;
@@ -646,6 +650,7 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
   CK(nm03::launch_preprocess(pre, params->median_window, hs, k1_mode, st));
   seg.pred = scratch;
   seg.dilated = d_out->dilated;
+  seg.dilated_bits = d_out->dilated_bits;
   seg.eroded = (params->erode_size > 0) ? d_out->eroded : nullptr;
   seg.rg_mask = d_out->rg_mask;
   seg.iterations = d_out->rg_iterations;
@@ -655,7 +660,7 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
 }
 
 const char* nm03_last_error(void) { return g_err; }
-int nm03_version(void) { return 100; }
+int nm03_version(void) { return 101; }   // 101: nm03_outputs.dilated_bits, async tickets
 
 void nm03_default_params(nm03_params* p) {
   if (!p) return;
@@ -723,7 +728,7 @@ int nm03_init(const int* gpu_ids, int n_gpus, nm03_ctx** out) {
     if (e == cudaSuccess) e = nm03::configure_kernels();
     for (auto& s : wk->slots) {
       if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
-      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming | (g_spin_wait ? 0 : cudaEventBlockingSync));
     }
     if (e != cudaSuccess) {
       nm03_shutdown(ctx);
@@ -802,6 +807,24 @@ int nm03_profile_read(nm03_ctx* ctx, int gpu, double* preprocess_ms, double* seg
   return NM03_OK;
 }
 
+long long nm03_profile_work(nm03_ctx* ctx, int gpu) {
+  Worker* wk;
+  if (get_worker(ctx, gpu, &wk)) return -1;
+  DeviceGuard g(wk->device);
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  unsigned long long total = 0;
+  for (auto& s : wk->slots) {
+    if (!s.sched) continue;
+    unsigned long long v = 0;
+    if (cudaMemcpy(&v, s.sched + 2, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    if (cudaMemset(s.sched + 2, 0, sizeof(v)) != cudaSuccess) return -1;
+    total += v;
+  }
+  return (long long)total;
+}
+
+int nm03_median_network_ops(int median_window) { return nm03::median_network_ops(median_window); }
+
 int nm03_host_alloc(void** p, size_t bytes) {
   if (!p) return fail(NM03_ERR_INVALID, "p is null");
   cudaError_t e = cudaHostAlloc(p, bytes, cudaHostAllocPortable);
@@ -829,6 +852,66 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
   return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out, true);
 }
 
+// One chunk [start, start+cnt) of a host-buffer batch on slot s: H2D copy, K1 + K23, D2H copies of every requested
+// output, and the slot's event recorded behind them.  n_total sizes the staging buffers (see below).
+static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start, int cnt, int n_total, int w, int h,
+                              const nm03_params* params, const int* seeds_xy, int n_seeds, const nm03_outputs* out) {
+  int rc;
+  const size_t npx = (size_t)w * h, wpr = (size_t)(w + 31) / 32;
+  // per-chunk device staging laid out as [inputs][dilated][eroded][rg_mask][sharpened][median][bits][iters]
+  size_t out_bytes = 0;
+  const size_t o_dil = out_bytes; if (out->dilated) out_bytes += cnt * npx;
+  const size_t o_ero = out_bytes; if (out->eroded) out_bytes += cnt * npx;
+  const size_t o_rg = out_bytes; if (out->rg_mask) out_bytes += cnt * npx;
+  out_bytes = (out_bytes + 15) & ~(size_t)15;
+  const size_t o_sh = out_bytes; if (out->sharpened) out_bytes += cnt * npx * 4;
+  const size_t o_med = out_bytes; if (out->median) out_bytes += cnt * npx * 4;
+  const size_t o_bits = out_bytes; if (out->dilated_bits) out_bytes += (size_t)cnt * h * wpr * 4;
+  const size_t o_it = out_bytes; if (out->rg_iterations) out_bytes += (size_t)cnt * 4;
+  // staging is sized for the whole batch even when the call works in chunks: the next batch of this shape may
+  // come unchunked, and growing a buffer then would put a cudaFree/cudaMalloc in its path
+  const size_t per_slice = npx * ((out->dilated ? 1 : 0) + (out->eroded ? 1 : 0) + (out->rg_mask ? 1 : 0) +
+                                  (out->sharpened ? 4 : 0) + (out->median ? 4 : 0)) + (out->dilated_bits ? h * wpr * 4 : 0) +
+                           (out->rg_iterations ? 4 : 0);
+  if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, (size_t)n_total * npx * 2))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n_total * per_slice + 32)))) return rc;
+  cudaStream_t st = s->stream;
+  cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
+                                  cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) return fail(NM03_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e));
+  uint8_t* so = (uint8_t*)s->stage_out;
+  nm03_outputs d = {};
+  if (out->dilated) d.dilated = so + o_dil;
+  if (out->eroded) d.eroded = so + o_ero;
+  if (out->rg_mask) d.rg_mask = so + o_rg;
+  if (out->sharpened) d.sharpened = (float*)(so + o_sh);
+  if (out->median) d.median = (float*)(so + o_med);
+  if (out->dilated_bits) d.dilated_bits = (uint32_t*)(so + o_bits);
+  if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
+  // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
+  if ((rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, false))) return rc;
+#define NM03_D2H(field, off, elem)                                                                          \
+  if (out->field && e == cudaSuccess)                                                                       \
+    e = cudaMemcpyAsync((uint8_t*)out->field + (size_t)start * npx * (elem), so + (off), cnt * npx * (elem), \
+                        cudaMemcpyDeviceToHost, st);
+  NM03_D2H(dilated, o_dil, 1)
+  NM03_D2H(eroded, o_ero, 1)
+  NM03_D2H(rg_mask, o_rg, 1)
+  NM03_D2H(sharpened, o_sh, 4)
+  NM03_D2H(median, o_med, 4)
+#undef NM03_D2H
+  if (out->dilated_bits && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->dilated_bits + (size_t)start * h * wpr, so + o_bits, (size_t)cnt * h * wpr * 4, cudaMemcpyDeviceToHost, st);
+  if (out->rg_iterations && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->rg_iterations + start, so + o_it, (size_t)cnt * 4, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
+  if (e != cudaSuccess) return fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e));
+  return NM03_OK;
+}
+
+// wait for everything queued on the slot so far (its event is recorded behind the last D2H copy)
+static cudaError_t wait_slot(Slot* s) { return cudaEventSynchronize(s->done); }
+
 int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
                        const int* seeds_xy, int n_seeds, const nm03_outputs* out, int* status) {
   Worker* wk;
@@ -841,10 +924,8 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
     return rc;
   }
   DeviceGuard g(wk->device);
-  const size_t npx = (size_t)w * h;
-  // Chunks of the batch are pipelined over the stream slots so that the H2D copy of one chunk, the
-  // kernels of another and the D2H copy of a third overlap.
-  // A lone caller gets its batch pipelined in chunks; when other host-buffer batches are in flight on this GPU they
+  // A lone caller gets its batch pipelined in chunks over the stream slots, so that the H2D copy of one chunk, the
+  // kernels of another and the D2H copy of a third overlap; when other host-buffer batches are in flight on this GPU they
   // already overlap each other's copies and kernels, and whole batches keep the H2D engine busier than interleaved
   // chunks do (3 feeder threads, 24 slices of 512x512: 96 000 slices/s unchunked, 84 000 in 4 chunks; one thread:
   // 63 500 in 4 chunks).
@@ -867,68 +948,68 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
     if (!s) {
       s = used.front();
       used.erase(used.begin());
-      cudaStreamSynchronize(s->stream);
+      wait_slot(s);
     }
     used.push_back(s);
-    // per-chunk device staging laid out as [inputs][dilated][eroded][rg_mask][sharpened][median][iters]
-    size_t out_bytes = 0;
-    const size_t o_dil = out_bytes; if (out->dilated) out_bytes += cnt * npx;
-    const size_t o_ero = out_bytes; if (out->eroded) out_bytes += cnt * npx;
-    const size_t o_rg = out_bytes; if (out->rg_mask) out_bytes += cnt * npx;
-    out_bytes = (out_bytes + 15) & ~(size_t)15;
-    const size_t o_sh = out_bytes; if (out->sharpened) out_bytes += cnt * npx * 4;
-    const size_t o_med = out_bytes; if (out->median) out_bytes += cnt * npx * 4;
-    const size_t o_it = out_bytes; if (out->rg_iterations) out_bytes += (size_t)cnt * 4;
-    // staging is sized for the whole batch even when this call works in chunks: the next batch of this shape may
-    // come unchunked (see above), and growing a buffer then would put a cudaFree/cudaMalloc in its path
-    const size_t per_slice = npx * ((out->dilated ? 1 : 0) + (out->eroded ? 1 : 0) + (out->rg_mask ? 1 : 0) +
-                                    (out->sharpened ? 4 : 0) + (out->median ? 4 : 0)) + (out->rg_iterations ? 4 : 0);
-    rc = ensure(s, &s->stage_in, &s->stage_in_bytes, (size_t)n * npx * 2);
-    if (!rc) rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n * per_slice + 32));
-    if (rc) { result = rc; break; }
-    cudaStream_t st = s->stream;
-    cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
-                                    cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "H2D copy failed: %s", cudaGetErrorString(e)); break; }
-    uint8_t* so = (uint8_t*)s->stage_out;
-    nm03_outputs d = {};
-    if (out->dilated) d.dilated = so + o_dil;
-    if (out->eroded) d.eroded = so + o_ero;
-    if (out->rg_mask) d.rg_mask = so + o_rg;
-    if (out->sharpened) d.sharpened = (float*)(so + o_sh);
-    if (out->median) d.median = (float*)(so + o_med);
-    if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
-    // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
-    rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, false);
-    if (rc) { result = rc; break; }
-#define NM03_D2H(field, off, elem)                                                                          \
-  if (out->field && e == cudaSuccess)                                                                       \
-    e = cudaMemcpyAsync((uint8_t*)out->field + (size_t)start * npx * (elem), so + (off), cnt * npx * (elem), \
-                        cudaMemcpyDeviceToHost, st);
-    NM03_D2H(dilated, o_dil, 1)
-    NM03_D2H(eroded, o_ero, 1)
-    NM03_D2H(rg_mask, o_rg, 1)
-    NM03_D2H(sharpened, o_sh, 4)
-    NM03_D2H(median, o_med, 4)
-#undef NM03_D2H
-    if (out->rg_iterations && e == cudaSuccess)
-      e = cudaMemcpyAsync(out->rg_iterations + start, so + o_it, (size_t)cnt * 4, cudaMemcpyDeviceToHost, st);
-    if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
-    if (e != cudaSuccess) { result = fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e)); break; }
+    if ((rc = enqueue_host_chunk(wk, s, slices, start, cnt, n, w, h, params, seeds_xy, n_seeds, out))) { result = rc; break; }
     // keep at most kChunksPerCall chunks in flight: the oldest slot is drained and handed back
     if ((int)used.size() == n_chunks) {
       Slot* old = used.front();
       used.erase(used.begin());
-      cudaStreamSynchronize(old->stream);
+      wait_slot(old);
       release(wk, old);
     }
   }
   for (Slot* s : used) {
-    cudaError_t e = cudaStreamSynchronize(s->stream);
+    cudaError_t e = s->used ? wait_slot(s) : cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess && result == NM03_OK) result = fail(NM03_ERR_CUDA, "pipeline failed: %s", cudaGetErrorString(e));
     release(wk, s);
   }
   if (status) for (int i = 0; i < n; ++i) status[i] = result;
+  return result;
+}
+
+struct nm03_ticket {
+  Worker* wk;
+  Slot* slot;      // held (busy) until nm03_wait
+  int result;      // error found while queueing (the slot is idle then)
+};
+
+int nm03_process_batch_async(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
+                             const int* seeds_xy, int n_seeds, const nm03_outputs* out, nm03_ticket** ticket) {
+  Worker* wk;
+  int rc;
+  if (!ticket) return fail(NM03_ERR_INVALID, "ticket is null");
+  *ticket = nullptr;
+  if ((rc = get_worker(ctx, gpu, &wk))) return rc;
+  if (!slices || !out || n <= 0) return fail(NM03_ERR_INVALID, "null buffer or no slices");
+  if ((rc = check_params(params, w, h, true))) return rc;
+  DeviceGuard g(wk->device);
+  Slot* s = acquire(wk, false);
+  if (!s) return fail(NM03_ERR_BUSY, "all %d stream slots of this GPU hold unfinished tickets; call nm03_wait on one first", kSlots);
+  wk->host_calls.fetch_add(1);
+  rc = enqueue_host_chunk(wk, s, slices, 0, n, n, w, h, params, seeds_xy, n_seeds, out);
+  if (rc) {   // nothing useful is in flight: drain what was queued and hand the slot back
+    cudaStreamSynchronize(s->stream);
+    wk->host_calls.fetch_sub(1);
+    release(wk, s);
+    return rc;
+  }
+  *ticket = new nm03_ticket{wk, s, NM03_OK};
+  return NM03_OK;
+}
+
+int nm03_wait(nm03_ticket* t) {
+  if (!t) return fail(NM03_ERR_INVALID, "ticket is null");
+  int result = t->result;
+  {
+    DeviceGuard g(t->wk->device);
+    cudaError_t e = wait_slot(t->slot);
+    if (e != cudaSuccess && result == NM03_OK) result = fail(NM03_ERR_CUDA, "pipeline failed: %s", cudaGetErrorString(e));
+  }
+  t->wk->host_calls.fetch_sub(1);
+  release(t->wk, t->slot);
+  delete t;
   return result;
 }
 

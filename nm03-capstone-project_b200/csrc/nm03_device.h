@@ -25,6 +25,9 @@ constexpr int K1_MW = K1_TW + 2 * K1_HS_MAX;      // 136 median columns
 constexpr int K1_MH = K1_TH + 2 * K1_HS_MAX;      // 72 median rows
 constexpr int K1_MHP = K1_MH / 2;                 // 36 packed median rows (row p and row p+36 share a register)
 constexpr int K1_PWS = 144;                       // packed raw tile row stride in words (>= 136 + 6, multiple of 4)
+// windows above 9x9 need a wider halo: their packed tile has a longer row and their TMA box starts further left
+__host__ __device__ constexpr int k1_pws(int K) { return K <= 9 ? K1_PWS : 160; }
+__host__ __device__ constexpr int k1_xbox(int K) { return K <= 9 ? 8 : 16; }
 constexpr int K1_THREADS = NM03_K1_THREADS;
 constexpr int K1_MIN_CTAS = NM03_K1_MIN_CTAS;                   // resident CTAs per SM the register budget is set for
 
@@ -39,7 +42,8 @@ struct PreParams {
   float clip_min, clip_max;
   float gain, rg_min, rg_max;
   int border_zero, use_fma, input_unsigned;
-  unsigned int* sched;   // optional [2], zero between launches: work counter + finished-CTA counter of the persistent grid
+  unsigned int* sched;   // optional [4]: work counter + finished-CTA counter of the persistent grid (zero between launches),
+                         // then a 64-bit running count of the median work items that were sorted (nm03_profile_work)
   const float* lut;      // optional [65536]: f(key) for every 16-bit key (bit-identical to the arithmetic), else null
   // windows whose samples all have key <= skip_key map to f() == skip_val, so their median is known
   // without sorting (clip floor; 0 = off).  skip_key2 = the key replicated in both 16-bit halves.
@@ -75,6 +79,7 @@ constexpr int SEG_MAX_CLUSTER = 8;
 struct SegParams {
   const uint32_t* pred;  // [n][h][wpr]: range predicate (do_fill=1) or the mask itself (do_fill=0)
   uint8_t* dilated;      // optional [n][h][w]
+  uint32_t* dilated_bits;  // optional [n][h][wpr]: the dilated mask bit-packed (bit x%32 of word x/32)
   uint8_t* eroded;       // optional
   uint8_t* rg_mask;      // optional
   int32_t* iterations;   // optional [n]
@@ -102,6 +107,7 @@ cudaError_t launch_threshold_pack(const float* img, int n, int w, int h, float l
                                   cudaStream_t s);
 cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* bits, cudaStream_t s);
 cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s);  // fills lut[65536] with f(key)
+int median_network_ops(int median_window);   // min/max instructions of one generated median work item (0 = no network)
 cudaError_t configure_kernels();  // opt in to large dynamic shared memory; once per device
 
 }  // namespace nm03

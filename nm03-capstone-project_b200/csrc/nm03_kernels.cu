@@ -98,6 +98,8 @@ __device__ __forceinline__ void load_window_row(const uint32_t* __restrict__ src
 
 template <int K>
 struct MedianRun;
+template <int K>
+struct MedianRunLen { static constexpr int value = 4; };   // windows without a generated network: runs of 4 outputs
 #define NM03_DEFINE_MEDIAN_RUN(K_)                                                                              \
   template <>                                                                                                   \
   struct MedianRun<K_> {                                                                                        \
@@ -111,6 +113,10 @@ NM03_DEFINE_MEDIAN_RUN(5)
 NM03_DEFINE_MEDIAN_RUN(7)
 NM03_DEFINE_MEDIAN_RUN(9)
 #undef NM03_DEFINE_MEDIAN_RUN
+template <> struct MedianRunLen<3> { static constexpr int value = MedianRun<3>::RUN; };
+template <> struct MedianRunLen<5> { static constexpr int value = MedianRun<5>::RUN; };
+template <> struct MedianRunLen<7> { static constexpr int value = MedianRun<7>::RUN; };
+template <> struct MedianRunLen<9> { static constexpr int value = MedianRun<9>::RUN; };
 
 // Unsharp mask for 4 horizontally adjacent pixels, accumulating exactly in the oracle's order
 // (tap x outer, tap y inner, from 0.0f; nm03o_sharpen).  M points at the median tile row of the
@@ -215,11 +221,17 @@ template <int K, int HS, int MODE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p,
                                                                          const __grid_constant__ CUtensorMap tmap) {
   constexpr int R = K / 2;
+  constexpr int PWS = k1_pws(K);           // packed raw tile row stride in words
+  constexpr int XB = k1_xbox(K);           // the TMA box starts XB pixels left of the output tile
+  constexpr bool NET = K <= 9;             // generated min/max network; larger windows use the generic rank search
   constexpr int PR = K1_MHP + 2 * R;       // packed raw rows
   constexpr int RW = K1_MW + 2 * R;        // raw columns actually needed
-  constexpr int RUN = MedianRun<K>::RUN;   // outputs (packed registers) per work item
+  constexpr int RUN = MedianRunLen<K>::value;   // outputs (packed registers) per work item
   constexpr int NRUN = K1_MW / RUN;
-  static_assert(RW <= K1_PWS, "packed tile stride too small");
+  // windows above 9x9 keep their keys in UNSIGNED order (signed key ^ 0x8000): the rank search compares with the
+  // unsigned packed min
+  constexpr uint32_t KFLIP = NET ? 0u : 0x8000u;
+  static_assert(RW <= PWS, "packed tile stride too small");
   static_assert(K1_MW % RUN == 0 && RUN % 2 == 0, "median tile width must be a multiple of the (even) run length");
 
   extern __shared__ __align__(16) uint32_t smem_raw[];
@@ -227,13 +239,13 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // compiler keeps the shared address space (LDS/STS with 32-bit addresses); rounding the pointer through uintptr_t
   // turned every tile access into a generic LD.E/ST.E with 64-bit address arithmetic.
   uint32_t* smem = smem_raw + (((128u - (smem_u32(smem_raw) & 127u)) & 127u) >> 2);
-  uint32_t* P = smem;                                         // [PR][K1_PWS] packed keys (row q | row q+36 <<16)
-  float* M = reinterpret_cast<float*>(smem + PR * K1_PWS);    // [K1_MH][K1_MW] f(median)
+  uint32_t* P = smem;                                         // [PR][PWS] packed keys (row q | row q+36 <<16)
+  float* M = reinterpret_cast<float*>(smem + PR * PWS);    // [K1_MH][K1_MW] f(median)
 
   constexpr int RH = K1_MH + 2 * R;
-  constexpr int OFF = 8 - K1_HS_MAX - R;   // TMA box starts at x0-8 (16-byte rule): raw column col sits at box column col + OFF
-  static_assert(OFF >= 0 && RW + OFF <= K1_PWS, "halo does not fit the aligned TMA box");
-  uint16_t* T = reinterpret_cast<uint16_t*>(M + K1_MH * K1_MW);   // [RH][K1_PWS] raw samples of the NEXT work item (TMA destination)
+  constexpr int OFF = XB - K1_HS_MAX - R;  // TMA box starts at x0-XB (16-byte rule): raw column col sits at box column col + OFF
+  static_assert(OFF >= 0 && RW + OFF <= PWS, "halo does not fit the aligned TMA box");
+  uint16_t* T = reinterpret_cast<uint16_t*>(M + K1_MH * K1_MW);   // [RH][PWS] raw samples of the NEXT work item (TMA destination)
   __shared__ __align__(8) uint64_t bar;
   __shared__ int s_next;
 
@@ -260,8 +272,8 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // to the CTA through shared memory (done by every thread it cost ~1900 cycles per item on the uniform datapath)
   __shared__ int s_dec[2][4];
   auto issue_tma = [&](int s_, int x_, int y_) {   // one thread: bulk tensor copy of the raw halo tile of a work item
-    mbar_expect_tx(&bar, RH * K1_PWS * 2);
-    tma_load_3d(T, &tmap, &bar, x_ - 8, y_ - K1_HS_MAX - R, s_);
+    mbar_expect_tx(&bar, RH * PWS * 2);
+    tma_load_3d(T, &tmap, &bar, x_ - XB, y_ - K1_HS_MAX - R, s_);
   };
 
   // let a dependent kernel (K23, launched with programmatic serialization) be scheduled while this
@@ -302,15 +314,15 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     if (!p.border_zero) {
       // 4 packed words per thread: pixels i..i+3 of row q (low halves) and of row q+36 (high halves);
       // the OFF-pixel shift is folded into the byte permutes
-      const uint32_t bias2 = bias | (bias << 16);
+      const uint32_t bias2 = (bias ^ KFLIP) | ((bias ^ KFLIP) << 16);
       const uint32_t* Tw = reinterpret_cast<const uint32_t*>(T);
 #pragma unroll 3
-      for (int idx = tid; idx < PR * (K1_PWS / 4); idx += K1_THREADS) {
-        const int q = idx / (K1_PWS / 4), c4 = idx - q * (K1_PWS / 4);
-        const int w0 = (4 * c4 + OFF) >> 1;                 // first 32-bit word holding pixel 4*c4 + OFF
-        const uint32_t* ra = Tw + q * (K1_PWS / 2) + w0;
-        const uint32_t* rb = Tw + (q + K1_MHP) * (K1_PWS / 2) + w0;
-        const bool last = w0 + 2 >= K1_PWS / 2;             // the word past the row end is never needed for real columns
+      for (int idx = tid; idx < PR * (PWS / 4); idx += K1_THREADS) {
+        const int q = idx / (PWS / 4), c4 = idx - q * (PWS / 4);
+        const int w0 = min((4 * c4 + OFF) >> 1, PWS / 2 - 2);   // first 32-bit word holding pixel 4*c4 + OFF (columns past RW are never used)
+        const uint32_t* ra = Tw + q * (PWS / 2) + w0;
+        const uint32_t* rb = Tw + (q + K1_MHP) * (PWS / 2) + w0;
+        const bool last = w0 + 2 >= PWS / 2;             // the word past the row end is never needed for real columns
         const uint32_t a0 = ra[0], a1 = ra[1], a2 = last ? 0u : ra[2];
         const uint32_t b0 = rb[0], b1 = rb[1], b2 = last ? 0u : rb[2];
         uint4 o;
@@ -322,7 +334,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
           o.z = __byte_perm(a1, b1, 0x7632); o.w = __byte_perm(a2, b2, 0x5410);
         }
         o.x ^= bias2; o.y ^= bias2; o.z ^= bias2; o.w ^= bias2;
-        *reinterpret_cast<uint4*>(P + q * K1_PWS + 4 * c4) = o;
+        *reinterpret_cast<uint4*>(P + q * PWS + 4 * c4) = o;
       }
     }
     if (!interior || p.border_zero) {
@@ -332,36 +344,36 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       auto key = [&](int col, int row) -> uint32_t {
         const int gx = gx0 + col, gy = gy0 + row;
         if (p.border_zero) {
-          if (gx < 0 || gy < 0 || gx >= w || gy >= h) return 0x8000u;
-          const uint32_t v = (T[row * K1_PWS + min(col + OFF, K1_PWS - 1)] ^ bias) & 0xffffu;
-          return v == 0x8000u ? 0x8001u : v;
+          if (gx < 0 || gy < 0 || gx >= w || gy >= h) return 0x8000u ^ KFLIP;
+          const uint32_t v = (T[row * PWS + min(col + OFF, PWS - 1)] ^ bias) & 0xffffu;
+          return (v == 0x8000u ? 0x8001u : v) ^ KFLIP;
         }
-        const int cx = clampi(clampi(gx, 0, w - 1) - gx0 + OFF, 0, K1_PWS - 1), cy = clampi(clampi(gy, 0, h - 1) - gy0, 0, RH - 1);
-        return (T[cy * K1_PWS + cx] ^ bias) & 0xffffu;
+        const int cx = clampi(clampi(gx, 0, w - 1) - gx0 + OFF, 0, PWS - 1), cy = clampi(clampi(gy, 0, h - 1) - gy0, 0, RH - 1);
+        return ((T[cy * PWS + cx] ^ bias) & 0xffffu) ^ KFLIP;
       };
       // columns [0, cl) and [cr, PWS) of the tile are outside the image; a packed row q holds image
       // rows gy0+q and gy0+q+36
-      const int cl = p.border_zero ? K1_PWS : max(0, -gx0), cr = p.border_zero ? K1_PWS : min(K1_PWS, w - gx0);
+      const int cl = p.border_zero ? PWS : max(0, -gx0), cr = p.border_zero ? PWS : min(PWS, w - gx0);
       const int warp = tid >> 5, ln = tid & 31;
       auto row_outside = [&](int q) { const int gya = gy0 + q, gyb = gya + K1_MHP; return gya < 0 || gyb >= h || gya >= h || gyb < 0 || p.border_zero; };
       // rows with a half above or below the image: the whole row, one warp per row
       for (int q = warp; q < PR; q += K1_THREADS / 32)
         if (row_outside(q))
-          for (int col = ln; col < K1_PWS; col += 32) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          for (int col = ln; col < PWS; col += 32) P[q * PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
       // the other rows: only the few columns left / right of the image, eight lanes per row (a side strip is 7-9 columns
       // wide for whole tiles, so a full warp per row would leave three quarters of its lanes idle)
-      if (cl > 0 || cr < K1_PWS) {
+      if (cl > 0 || cr < PWS) {
         const int grp = tid >> 3, gl = tid & 7;
         for (int q = grp; q < PR; q += K1_THREADS / 8) {
           if (row_outside(q)) continue;
-          for (int col = gl; col < cl; col += 8) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
-          for (int col = cr + gl; col < K1_PWS; col += 8) P[q * K1_PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          for (int col = gl; col < cl; col += 8) P[q * PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
+          for (int col = cr + gl; col < PWS; col += 8) P[q * PWS + col] = key(col, q) | (key(col, q + K1_MHP) << 16);
         }
       }
     }
   } else {
-    for (int idx = tid; idx < PR * K1_PWS; idx += K1_THREADS) {
-      const int q = idx / K1_PWS, col = idx - q * K1_PWS;
+    for (int idx = tid; idx < PR * PWS; idx += K1_THREADS) {
+      const int q = idx / PWS, col = idx - q * PWS;
       uint32_t a, b;
       if (p.border_zero) {
         a = fetch_key<true>(img, w, h, gx0 + col, gy0 + q, bias);
@@ -370,7 +382,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         a = fetch_key<false>(img, w, h, gx0 + col, gy0 + q, bias);
         b = fetch_key<false>(img, w, h, gx0 + col, gy0 + q + K1_MHP, bias);
       }
-      P[idx] = a | (b << 16);
+      P[idx] = (a | (b << 16)) ^ (KFLIP | (KFLIP << 16));
     }
   }
   NM03_STAMP(1);
@@ -388,23 +400,23 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // Work items (packed row, run of 8 columns).  An item whose whole input footprint lies at or below
   // the clip floor has a known result (skip_val) and is not sorted: 8x8-block maxima of the packed
   // tile decide that, and the remaining items are compacted into a list so that warps stay full.
-  __shared__ uint32_t blkmax[(PR + 7) / 8][K1_PWS / 8];
-  __shared__ uint16_t worklist[K1_MHP * NRUN];
+  __shared__ uint32_t blkmax[NET ? (PR + 7) / 8 : 1][NET ? PWS / 8 : 1];
+  __shared__ uint16_t worklist[NET ? K1_MHP * NRUN : 1];
   __shared__ int n_work;
-  if (p.skip_on) {
+  if constexpr (NET) if (p.skip_on) {
     if (tid == 0) n_work = 0;
-    constexpr int NBLK = ((PR + 7) / 8) * (K1_PWS / 8);
+    constexpr int NBLK = ((PR + 7) / 8) * (PWS / 8);
     for (int base = 0; base < 2 * NBLK; base += K1_THREADS) {   // two threads per 8x8 block, four rows each (block-uniform trips)
       const int bidx = (base + tid) >> 1, half = tid & 1;
-      const int g = bidx / (K1_PWS / 8), c8 = bidx - g * (K1_PWS / 8);
+      const int g = bidx / (PWS / 8), c8 = bidx - g * (PWS / 8);
       uint32_t m = 0x80008000u;  // (-32768, -32768)
       if (bidx < NBLK) {
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) {
           const int q = 8 * g + 4 * half + qq;
           if (q < PR) {
-            const uint4 a = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8);
-            const uint4 c = *reinterpret_cast<const uint4*>(P + q * K1_PWS + 8 * c8 + 4);
+            const uint4 a = *reinterpret_cast<const uint4*>(P + q * PWS + 8 * c8);
+            const uint4 c = *reinterpret_cast<const uint4*>(P + q * PWS + 8 * c8 + 4);
             m = __vimax3_s16x2(m, __vmaxs2(a.x, a.y), __vmaxs2(a.z, a.w));
             m = __vimax3_s16x2(m, __vmaxs2(c.x, c.y), __vmaxs2(c.z, c.w));
           }
@@ -468,20 +480,83 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     __syncthreads();
   }
   NM03_STAMP(3);
-  const int n_items = p.skip_on ? n_work : K1_MHP * NRUN;
+  const int n_items = (NET && p.skip_on) ? n_work : K1_MHP * NRUN;
+  if (tid == 0 && p.sched) atomicAdd(reinterpret_cast<unsigned long long*>(p.sched + 2), (unsigned long long)n_items);   // nm03_profile_work
+  // windows above 9x9: every key of the tile shares the bits above the highest bit in which any two of them differ
+  // (12-bit data in a 16-bit word: the top four), so the rank search below starts there
+  __shared__ uint32_t s_diff;
+  int hb = -1;
+  uint32_t prefix2 = 0u;
+  if constexpr (!NET) {
+    if (tid == 0) s_diff = 0u;
+    __syncthreads();
+    const uint32_t ref = P[0] & 0xffffu, ref2 = ref | (ref << 16);
+    uint32_t d = 0u;
+    for (int i = tid; i < PR * (PWS / 4); i += K1_THREADS) {
+      const uint4 q4 = *reinterpret_cast<const uint4*>(P + 4 * i);
+      d |= (q4.x ^ ref2) | (q4.y ^ ref2) | (q4.z ^ ref2) | (q4.w ^ ref2);
+    }
+    d = __reduce_or_sync(0xffffffffu, (d | (d >> 16)) & 0xffffu);
+    if ((tid & 31) == 0 && d) atomicOr(&s_diff, d);
+    __syncthreads();
+    hb = 31 - __clz((int)s_diff);                       // -1: all keys equal
+    const uint32_t low = hb < 0 ? 0u : ((2u << hb) - 1u);
+    prefix2 = (ref & ~low) | ((ref & ~low) << 16);
+  }
   for (int wi = tid; wi < n_items; wi += K1_THREADS) {
-    const int it = p.skip_on ? worklist[wi] : wi;
+    int it = wi;
+    if constexpr (NET) { if (p.skip_on) it = worklist[wi]; }
     const int prow = it / NRUN, run = it - prow * NRUN;
-    uint32_t v[RUN + K - 1][K], o[RUN];
-    const uint32_t* src = P + prow * K1_PWS + run * RUN;
+    uint32_t o[RUN];
+    const uint32_t* src = P + prow * PWS + run * RUN;
+    if constexpr (NET) {
+      uint32_t v[RUN + K - 1][K];
 #pragma unroll
-    for (int r = 0; r < K; ++r) load_window_row<RUN + K - 1, RUN, K>(src + r * K1_PWS, v, r);
+      for (int r = 0; r < K; ++r) load_window_row<RUN + K - 1, RUN, K>(src + r * PWS, v, r);
 #ifdef NM03_TUNE_SKIP_B   // tuning builds only (tools/README.md): the window centre instead of the median
 #pragma unroll
-    for (int i = 0; i < RUN; ++i) o[i] = v[i + R][R];
+      for (int i = 0; i < RUN; ++i) o[i] = v[i + R][R];
 #else
-    MedianRun<K>::run(v, o);
+      MedianRun<K>::run(v, o);
 #endif
+    } else {
+      // Generic exact median for any odd window (11, 13, 15): most-significant-bit-first search for the value of rank
+      // (K*K+1)/2.  For a trial value t the number of window samples below t is counted with packed operations —
+      // min(x,t) ^ t is zero in a 16-bit half iff x >= t there, and min(.,1) turns that into 0/1 — for both pixels of a
+      // packed word at once and for RUN adjacent outputs that share the loaded rows.  Slower than the networks
+      // (about 16 * K*K * 1.75 instructions per pixel) but data-independent and exact, ties included.
+      constexpr uint32_t RANK = (K * K + 1) / 2;
+      constexpr int NC = RUN + K - 1, NC4 = (NC + 3) / 4;
+      static_assert(RUN == 4 && 4 * (K1_MW / RUN - 1) + 4 * NC4 <= PWS, "row loads of the rank search must stay inside the packed row");
+      uint32_t cand[RUN];
+#pragma unroll
+      for (int i = 0; i < RUN; ++i) cand[i] = prefix2;
+      for (int b = hb; b >= 0; --b) {
+        const uint32_t bit2 = (1u << b) * 0x00010001u;
+        uint32_t t[RUN], cnt[RUN];
+#pragma unroll
+        for (int i = 0; i < RUN; ++i) { t[i] = cand[i] | bit2; cnt[i] = 0u; }
+#pragma unroll 1
+        for (int r = 0; r < K; ++r) {
+          uint32_t x[4 * NC4];
+#pragma unroll
+          for (int c = 0; c < NC4; ++c) {
+            const uint4 q4 = *reinterpret_cast<const uint4*>(src + r * PWS + 4 * c);
+            x[4 * c] = q4.x; x[4 * c + 1] = q4.y; x[4 * c + 2] = q4.z; x[4 * c + 3] = q4.w;
+          }
+#pragma unroll
+          for (int c = 0; c < NC; ++c)
+#pragma unroll
+            for (int i = 0; i < RUN; ++i)
+              if (c >= i && c < i + K) cnt[i] += __vminu2(__vminu2(x[c], t[i]) ^ t[i], 0x00010001u);
+        }
+#pragma unroll
+        for (int i = 0; i < RUN; ++i)   // fewer than RANK samples below t: the median is at least t
+          cand[i] |= ((cnt[i] & 0xffffu) < RANK ? (1u << b) : 0u) | ((cnt[i] >> 16) < RANK ? (0x10000u << b) : 0u);
+      }
+#pragma unroll
+      for (int i = 0; i < RUN; ++i) o[i] = cand[i] ^ 0x80008000u;   // back to the signed key order the table is indexed by
+    }
     float lo[RUN], hi[RUN];
     if (p.lut) {
 #pragma unroll
@@ -1140,7 +1215,7 @@ static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
   if ((p.w & 7) || ((uintptr_t)p.in & 15) || !encode_tiled_fn()) return false;
     const cuuint64_t dims[3] = {(cuuint64_t)p.w, (cuuint64_t)p.h, (cuuint64_t)p.n};
   const cuuint64_t strides[2] = {(cuuint64_t)p.w * 2, (cuuint64_t)p.w * p.h * 2};
-  const cuuint32_t box[3] = {(cuuint32_t)K1_PWS, (cuuint32_t)(K1_MH + 2 * R), 1};
+  const cuuint32_t box[3] = {(cuuint32_t)k1_pws(2 * R + 1), (cuuint32_t)(K1_MH + 2 * R), 1};
   const cuuint32_t estr[3] = {1, 1, 1};
   return encode_tiled_fn()(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<void*>(p.in), dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -1150,12 +1225,12 @@ static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
 template <int K, int HS, int MODE>
 static cudaError_t launch_k1m(const PreParams& p0, cudaStream_t s) {
   constexpr int R = K / 2;
-  const size_t smem = (size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 128;
+  const size_t smem = (size_t)(K1_MHP + 2 * R) * k1_pws(K) * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * k1_pws(K) * 2 + 128;
   PreParams p = p0;
   CUtensorMap map;
   memset(&map, 0, sizeof(map));
   p.use_tma = p0.use_tma && make_tmap(p, R, &map);
-  if constexpr (MODE != K1_EXACT) {
+  if constexpr (MODE != K1_EXACT && K <= 9) {
     if (g_k1_ws && p.use_tma && !p.border_zero) return launch_k1_ws<K, HS, MODE>(p, map, s);
   }
   // persistent grid: at most one CTA per resident slot (K1_MIN_CTAS per SM), each loops over work items
@@ -1180,13 +1255,13 @@ static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
-  {
+  if constexpr (K <= 9) {
     cudaError_t e2 = cudaFuncSetAttribute(k1_ws<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem_bytes<K>());
     if (e2 == cudaSuccess && HS > 2)
       e2 = cudaFuncSetAttribute(k1_ws<K, HS, (HS > 2 ? K1_FAST_HE2 : K1_FAST_FULL)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ws_smem_bytes<K>());
     if (e2 != cudaSuccess) return e2;
   }
-  const int smem = (int)((size_t)(K1_MHP + 2 * R) * K1_PWS * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * K1_PWS * 2 + 128);
+  const int smem = (int)((size_t)(K1_MHP + 2 * R) * k1_pws(K) * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * k1_pws(K) * 2 + 128);
   cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess && HS > 2)
@@ -1204,8 +1279,24 @@ static cudaError_t config_k1() {
     case 73: return FN<7, 3>(__VA_ARGS__); case 74: return FN<7, 4>(__VA_ARGS__);                   \
     case 91: return FN<9, 1>(__VA_ARGS__); case 92: return FN<9, 2>(__VA_ARGS__);                   \
     case 93: return FN<9, 3>(__VA_ARGS__); case 94: return FN<9, 4>(__VA_ARGS__);                   \
+    case 111: return FN<11, 1>(__VA_ARGS__); case 112: return FN<11, 2>(__VA_ARGS__);               \
+    case 113: return FN<11, 3>(__VA_ARGS__); case 114: return FN<11, 4>(__VA_ARGS__);               \
+    case 131: return FN<13, 1>(__VA_ARGS__); case 132: return FN<13, 2>(__VA_ARGS__);               \
+    case 133: return FN<13, 3>(__VA_ARGS__); case 134: return FN<13, 4>(__VA_ARGS__);               \
+    case 151: return FN<15, 1>(__VA_ARGS__); case 152: return FN<15, 2>(__VA_ARGS__);               \
+    case 153: return FN<15, 3>(__VA_ARGS__); case 154: return FN<15, 4>(__VA_ARGS__);               \
     default: return cudaErrorInvalidValue;                                                          \
   }
+
+int median_network_ops(int median_window) {
+  switch (median_window) {
+    case 3: return NM03_MEDIAN_OPS_3;
+    case 5: return NM03_MEDIAN_OPS_5;
+    case 7: return NM03_MEDIAN_OPS_7;
+    case 9: return NM03_MEDIAN_OPS_9;
+    default: return 0;
+  }
+}
 
 cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, int mode, cudaStream_t s) {
   NM03_K1_DISPATCH(launch_k1, p, mode, s)
@@ -1465,7 +1556,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
   if (p.iterations && rank == 0 && tid == 0) p.iterations[slice] = passes;
 
   // ---- halo rows of the final mask for the structuring element --------------------------------
-  const int nmax = max(p.dilated ? p.dil_n : 0, p.eroded ? p.ero_n : 0);
+  const int nmax = max((p.dilated || p.dilated_bits) ? p.dil_n : 0, p.eroded ? p.ero_n : 0);
   if (C > 1) {
     cluster.sync();  // all masks final (also orders the do_fill = 0 copy)
     for (int i = tid; i < 2 * nmax * wpr; i += SEG_THREADS) {
@@ -1491,7 +1582,7 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
     const uint32_t m = MROW(r)[k];
     const bool has_l = k > 0, has_r = k < wpr - 1;
     if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
-    if (p.dilated) {
+    if (p.dilated || p.dilated_bits) {
       uint32_t acc = m;
       if (p.dil_n == 1 && p.dil_hw[0] == 0 && p.dil_hw[1] == 1) {   // Dilation(3) with the disc SE: the 5-pixel plus
         const uint32_t* row = MROW(r);
@@ -1510,7 +1601,9 @@ __global__ void __launch_bounds__(SEG_THREADS, 1) k23_segment(const __grid_const
           for (int s2 = 1; s2 <= hw; ++s2) acc |= __funnelshift_r(c, rr, s2) | __funnelshift_l(l, c, s2);
         }
       }
-      store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+      if (p.dilated) store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+      if (p.dilated_bits)   // dilation may have set bits beyond the last pixel of the row: they are not part of the image
+        p.dilated_bits[((size_t)slice * p.h + y) * wpr + k] = (k == wpr - 1 && (p.w & 31)) ? acc & ((1u << (p.w & 31)) - 1u) : acc;
     }
     if (p.eroded) {
       uint32_t acc = m;
@@ -1625,7 +1718,7 @@ __global__ void k3_global_morph(const __grid_constant__ SegParams p, const uint3
     const size_t rowoff = ((size_t)slice * p.h + y) * p.w;
     const uint32_t m = word(y, k);
     if (p.rg_mask) store_word_u8(p.rg_mask + rowoff, k * 32, p.w, m, vec);
-    if (p.dilated) {
+    if (p.dilated || p.dilated_bits) {
       uint32_t acc = p.dil_n > 0 ? 0u : m;
       for (int b = -p.dil_n; b <= p.dil_n && p.dil_n > 0; ++b) {
         if (y + b < 0 || y + b >= p.h) continue;
@@ -1634,7 +1727,9 @@ __global__ void k3_global_morph(const __grid_constant__ SegParams p, const uint3
         acc |= c;
         for (int s2 = 1; s2 <= hw; ++s2) acc |= __funnelshift_r(c, rr, s2) | __funnelshift_l(l, c, s2);
       }
-      store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+      if (p.dilated) store_word_u8(p.dilated + rowoff, k * 32, p.w, acc, vec);
+      if (p.dilated_bits)
+        p.dilated_bits[((size_t)slice * p.h + y) * wpr + k] = (k == wpr - 1 && (p.w & 31)) ? acc & ((1u << (p.w & 31)) - 1u) : acc;
     }
     if (p.eroded) {
       uint32_t acc = m;
@@ -1737,7 +1832,7 @@ cudaError_t launch_pack_u8(const uint8_t* mask, int n, int w, int h, uint32_t* b
 cudaError_t configure_kernels() {
   cudaError_t e;
   int median_window, sharpen_half;
-  for (median_window = 3; median_window <= 9; median_window += 2)
+  for (median_window = 3; median_window <= 15; median_window += 2)
     for (sharpen_half = 1; sharpen_half <= 4; ++sharpen_half) {
       e = [&]() -> cudaError_t { NM03_K1_DISPATCH(config_k1) }();
       if (e != cudaSuccess) return e;

@@ -72,17 +72,18 @@ inline Element read_header(Cursor& c, bool explicit_vr) {
 }
 
 // skip a sequence / item of undefined length by walking its content
-inline void skip_undefined(Cursor& c, bool explicit_vr, bool is_item) {
+inline void skip_undefined(Cursor& c, bool explicit_vr, bool is_item, int depth = 0) {
+  if (depth > 32) throw std::runtime_error("DICOM: sequences nested deeper than 32 levels");   // untrusted input: bound the recursion
   for (;;) {
     Element e = read_header(c, explicit_vr);
     if (e.group == 0xFFFE && e.elem == 0xE0DD && !is_item) return;  // sequence delimitation
     if (e.group == 0xFFFE && e.elem == 0xE00D && is_item) return;   // item delimitation
     if (e.group == 0xFFFE && e.elem == 0xE000) {                     // item
-      if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, true);
+      if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, true, depth + 1);
       else { if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated item"); c.off += e.len; }
       continue;
     }
-    if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, false);
+    if (e.len == 0xFFFFFFFFu) skip_undefined(c, explicit_vr, false, depth + 1);
     else { if (!c.has(e.len)) throw std::runtime_error("DICOM: truncated element"); c.off += e.len; }
   }
 }
@@ -107,7 +108,23 @@ struct View {
 // Throws NeedMore if the header does not fit in `size` bytes.
 struct NeedMore : std::runtime_error { NeedMore() : std::runtime_error("DICOM: header longer than the bytes read") {} };
 
+inline View parse_view_impl(const uint8_t* data, size_t size, size_t total);
+
 inline View parse_view(const uint8_t* data, size_t size, size_t total = 0) {
+  if (total <= size) return parse_view_impl(data, size, size);
+  // Only the head of the file is in memory: an element header or a nested sequence that straddles the end of the
+  // buffer looks like a truncated file to the parser.  Any such error means "read more", not "bad file".
+  try {
+    return parse_view_impl(data, size, total);
+  } catch (const NeedMore&) {
+    throw;
+  } catch (const std::runtime_error& e) {
+    if (std::strstr(e.what(), "truncated")) throw NeedMore();
+    throw;
+  }
+}
+
+inline View parse_view_impl(const uint8_t* data, size_t size, size_t total) {
   using namespace detail;
   if (total < size) total = size;
   const bool partial = total > size;
@@ -174,7 +191,35 @@ inline View parse_view(const uint8_t* data, size_t size, size_t total = 0) {
   throw std::runtime_error("DICOM: no pixel data element");
 }
 
-// Parse a Part-10 file image held in memory (header + a copy of the pixels).
+// Modality LUT (PS3.3 C.11.1): value = RescaleSlope * stored + RescaleIntercept.  FAST's importer hands the pipeline
+// the pixel values DCMTK reports (src/sequential/main_sequential.cpp:175-186), which include this step, so it is
+// applied here, in place, before the slice goes to the GPU.  The pipeline's input is a 16-bit integer image: slope and
+// intercept must be integers and every rescaled value must fit the output type — signed 16 bit when the stored values
+// are signed or the intercept is negative, unsigned 16 bit otherwise.  Anything else is refused with a clear error
+// rather than segmented from the wrong values.  Returns the pixel representation of the result (0 unsigned, 1 signed).
+inline int rescaled_representation(int pixel_representation, double slope, double intercept) {
+  if (slope == 1.0 && intercept == 0.0) return pixel_representation;
+  return (pixel_representation == 1 || intercept < 0.0) ? 1 : 0;
+}
+
+inline int rescale_in_place(uint16_t* px, size_t n, int pixel_representation, double slope, double intercept) {
+  if (slope == 1.0 && intercept == 0.0) return pixel_representation;
+  if (slope != (double)(long long)slope || intercept != (double)(long long)intercept || slope == 0.0)
+    throw std::runtime_error("DICOM: RescaleSlope " + std::to_string(slope) + " / RescaleIntercept " + std::to_string(intercept) +
+                             " is not supported (integer slope and intercept only)");
+  const long long a = (long long)slope, b = (long long)intercept;
+  const int out_rep = rescaled_representation(pixel_representation, slope, intercept);
+  const long long lo = out_rep ? -32768 : 0, hi = out_rep ? 32767 : 65535;
+  for (size_t i = 0; i < n; ++i) {
+    const long long stored = pixel_representation ? (long long)(int16_t)px[i] : (long long)px[i];
+    const long long v = a * stored + b;
+    if (v < lo || v > hi) throw std::runtime_error("DICOM: rescaled pixel value " + std::to_string(v) + " does not fit 16 bits");
+    px[i] = (uint16_t)(int64_t)v;
+  }
+  return out_rep;
+}
+
+// Parse a Part-10 file image held in memory (header + a copy of the pixels; the modality LUT is applied).
 inline Slice parse(const uint8_t* data, size_t size) {
   const View v = parse_view(data, size);
   Slice s;
@@ -182,6 +227,7 @@ inline Slice parse(const uint8_t* data, size_t size) {
   s.rescale_slope = v.rescale_slope; s.rescale_intercept = v.rescale_intercept; s.instance_number = v.instance_number;
   s.pixels.resize((size_t)v.rows * v.cols);
   std::memcpy(s.pixels.data(), data + v.pixel_offset, v.pixel_bytes);  // little endian host assumed (x86-64 / aarch64)
+  s.pixel_representation = rescale_in_place(s.pixels.data(), s.pixels.size(), v.pixel_representation, v.rescale_slope, v.rescale_intercept);
   return s;
 }
 
@@ -273,7 +319,7 @@ struct Out {
 }  // namespace detail
 
 inline std::vector<uint8_t> encode(const uint16_t* pixels, int cols, int rows, bool is_signed, int instance_number,
-                                   bool explicit_vr = true) {
+                                   bool explicit_vr = true, const std::string& slope = "1", const std::string& intercept = "0") {
   using detail::Out;
   const std::string ts = explicit_vr ? "1.2.840.10008.1.2.1" : "1.2.840.10008.1.2";
   Out meta;
@@ -301,15 +347,15 @@ inline std::vector<uint8_t> encode(const uint16_t* pixels, int cols, int rows, b
   o.us(ex, 0x0028, 0x0101, 16);
   o.us(ex, 0x0028, 0x0102, 15);
   o.us(ex, 0x0028, 0x0103, is_signed ? 1 : 0);
-  o.str(ex, 0x0028, 0x1052, "DS", "0");
-  o.str(ex, 0x0028, 0x1053, "DS", "1");
+  o.str(ex, 0x0028, 0x1052, "DS", intercept);
+  o.str(ex, 0x0028, 0x1053, "DS", slope);
   o.elem(ex, 0x7FE0, 0x0010, "OW", pixels, (uint32_t)((size_t)rows * cols * 2));
   return o.b;
 }
 
 inline void save(const std::string& path, const uint16_t* pixels, int cols, int rows, bool is_signed, int instance_number,
-                 bool explicit_vr = true) {
-  const std::vector<uint8_t> b = encode(pixels, cols, rows, is_signed, instance_number, explicit_vr);
+                 bool explicit_vr = true, const std::string& slope = "1", const std::string& intercept = "0") {
+  const std::vector<uint8_t> b = encode(pixels, cols, rows, is_signed, instance_number, explicit_vr, slope, intercept);
   std::ofstream f(path, std::ios::binary);
   if (!f || !f.write((const char*)b.data(), (std::streamsize)b.size())) throw std::runtime_error("cannot write " + path);
 }

@@ -16,6 +16,23 @@ int nm03h_dicom_write(const char* path, const uint16_t* px, int cols, int rows, 
   catch (const std::exception& e) { if (err) std::strncpy(err, e.what(), errlen - 1); return -1; }
 }
 
+// same, with RescaleSlope / RescaleIntercept written as the given decimal strings
+int nm03h_dicom_write_rescale(const char* path, const uint16_t* px, int cols, int rows, int is_signed, int instance, int explicit_vr,
+                              const char* slope, const char* intercept, char* err, int errlen) {
+  try { nm03::dicom::save(path, px, cols, rows, is_signed != 0, instance, explicit_vr != 0, slope, intercept); return 0; }
+  catch (const std::exception& e) { if (err) { std::strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return -1; }
+}
+
+// header through the positional reader the batch driver uses (first 16 KiB, the whole file only when needed)
+int nm03h_dicom_view(const char* path, int* cols, int* rows, long* pixel_offset, char* err, int errlen) {
+  try {
+    nm03::dicom::FileReader r(path);
+    const nm03::dicom::View v = r.view();
+    *cols = v.cols; *rows = v.rows; *pixel_offset = (long)v.pixel_offset;
+    return 0;
+  } catch (const std::exception& e) { if (err) { std::strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return -1; }
+}
+
 // first call with px = NULL to get the size
 int nm03h_dicom_read(const char* path, int* cols, int* rows, int* is_signed, int* instance, uint16_t* px, long cap,
                      char* err, int errlen) {

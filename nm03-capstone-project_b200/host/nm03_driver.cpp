@@ -224,23 +224,29 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     std::vector<int> idx;
     for (int j = first; j < n && (int)idx.size() < opt.batch; ++j)
       if (!done[j] && state[j] == 0 && slices[j].cols == slices[first].cols && slices[j].rows == slices[first].rows &&
-          slices[j].pixel_representation == slices[first].pixel_representation) { idx.push_back(j); done[j] = 1; }
+          slices[j].pixel_representation == slices[first].pixel_representation &&
+          slices[j].rescale_slope == slices[first].rescale_slope && slices[j].rescale_intercept == slices[first].rescale_intercept) { idx.push_back(j); done[j] = 1; }
     const int w = slices[first].cols, h = slices[first].rows, m = (int)idx.size();
     const size_t npx = (size_t)w * h;
     in.reserve(m * npx * 2);
     out.reserve(m * npx);
     std::atomic<int> read_failed{0};
     parallel_for(m, opt.host_threads, [&](int j) {
-      try { readers[idx[j]].read_at((uint8_t*)in.p + j * npx * 2, npx * 2, slices[idx[j]].pixel_offset); }
-      catch (const std::exception&) { read_failed = 1; }
+      try {
+        readers[idx[j]].read_at((uint8_t*)in.p + j * npx * 2, npx * 2, slices[idx[j]].pixel_offset);
+        // modality LUT (identity for almost every MR file: then nothing is touched)
+        nm03::dicom::rescale_in_place((uint16_t*)((uint8_t*)in.p + j * npx * 2), npx, slices[idx[j]].pixel_representation,
+                                      slices[idx[j]].rescale_slope, slices[idx[j]].rescale_intercept);
+      } catch (const std::exception& e) {
+        read_failed = 1;
+        std::lock_guard<std::mutex> lk(tot.log);
+        std::cerr << "Error processing file " << files[idx[j]] << ":\nDetailed error: " << e.what() << std::endl;
+      }
     });
-    if (read_failed) {
-      std::lock_guard<std::mutex> lk(tot.log);
-      std::cerr << "Error processing patient " << patient << ": short read of pixel data" << std::endl;
-      continue;
-    }
+    if (read_failed) continue;   // the group is skipped, the patient goes on (main_parallel.cpp:163-167)
     timer.lap(tot.ns_read);
-    params.input_unsigned = slices[first].pixel_representation == 0;
+    params.input_unsigned = nm03::dicom::rescaled_representation(slices[first].pixel_representation, slices[first].rescale_slope,
+                                                                 slices[first].rescale_intercept) == 0;
     nm03_outputs o = {};
     o.dilated = (uint8_t*)out.p;
     std::vector<int> status(m, 0);

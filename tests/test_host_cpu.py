@@ -86,6 +86,87 @@ def test_dicom_rejects_bad_files(host, tmp_path):
         _read(host, str(tmp_path / "missing.dcm"))
 
 
+def _write_rescaled(host, path, img, signed, slope, intercept):
+    err = C.create_string_buffer(256)
+    h, w = img.shape
+    assert host.nm03h_dicom_write_rescale(path.encode(), img.ctypes.data_as(C.c_void_p), w, h, signed, 1, 1, slope.encode(),
+                                          intercept.encode(), err, 256) == 0, err.value
+
+
+def test_dicom_modality_lut_is_applied(host, tmp_path):
+    """RescaleSlope / RescaleIntercept (0028,1053 / 0028,1052): the importer hands on slope * stored + intercept, as DCMTK
+    does for FAST's importer; the result is signed when the intercept is negative."""
+    rng = np.random.default_rng(5)
+    stored = rng.integers(0, 4096, (100, 120)).astype(np.uint16)
+    path = str(tmp_path / "ct.dcm")
+    _write_rescaled(host, path, stored, 0, "1", "-1024")
+    px, sgn, _ = _read(host, path)
+    assert sgn == 1
+    np.testing.assert_array_equal(px.view(np.int16), stored.astype(np.int32) - 1024)
+    _write_rescaled(host, path, stored, 0, "2.0", "10")
+    px, sgn, _ = _read(host, path)
+    assert sgn == 0
+    np.testing.assert_array_equal(px, 2 * stored.astype(np.int32) + 10)
+    _write_rescaled(host, path, stored, 0, "1", "0")
+    px, sgn, _ = _read(host, path)
+    assert sgn == 0
+    np.testing.assert_array_equal(px, stored)
+
+
+def test_dicom_unsupported_rescale_is_refused(host, tmp_path):
+    stored = np.full((100, 100), 4000, np.uint16)
+    path = str(tmp_path / "r.dcm")
+    _write_rescaled(host, path, stored, 0, "0.5", "0")
+    with pytest.raises(RuntimeError, match="integer slope and intercept only"):
+        _read(host, path)
+    _write_rescaled(host, path, stored, 0, "20", "0")          # 80 000 does not fit 16 bits
+    with pytest.raises(RuntimeError, match="does not fit 16 bits"):
+        _read(host, path)
+
+
+def _view(host, path):
+    cols, rows, off = C.c_int(), C.c_int(), C.c_long()
+    err = C.create_string_buffer(256)
+    if host.nm03h_dicom_view(path.encode(), C.byref(cols), C.byref(rows), C.byref(off), err, 256):
+        raise RuntimeError(err.value.decode())
+    return cols.value, rows.value, off.value
+
+
+@pytest.mark.parametrize("pad", [16384 - 700, 16384 - 640, 16384 - 600, 40000])
+def test_positional_reader_rereads_when_the_header_straddles_its_first_block(host, tmp_path, pad):
+    """The batch driver parses the first 16 KiB of a file; an element header or an undefined-length sequence cut by that
+    boundary must lead to a second, whole-file read — not to a 'truncated' error."""
+    img = np.arange(100 * 100, dtype=np.uint16).reshape(100, 100)
+    path = str(tmp_path / "a.dcm")
+    err = C.create_string_buffer(256)
+    assert host.nm03h_dicom_write(path.encode(), img.ctypes.data_as(C.c_void_p), 100, 100, 0, 1, 1, err, 256) == 0
+    raw = bytearray(open(path, "rb").read())
+    pos = raw.find(struct.pack("<HH", 0x7FE0, 0x0010))
+    filler = struct.pack("<HH2sHI", 0x0009, 0x1002, b"OB", 0, pad) + b"\0" * pad       # pushes what follows to the boundary
+    item = struct.pack("<HH2sH", 0x0008, 0x0100, b"SH", 4) + b"ABCD"
+    seq = (struct.pack("<HH2sHI", 0x0009, 0x1001, b"SQ", 0, 0xFFFFFFFF) + struct.pack("<HHI", 0xFFFE, 0xE000, 0xFFFFFFFF) + item * 6
+           + struct.pack("<HHI", 0xFFFE, 0xE00D, 0) + struct.pack("<HHI", 0xFFFE, 0xE0DD, 0))
+    raw[pos:pos] = filler + seq
+    open(path, "wb").write(raw)
+    cols, rows, off = _view(host, path)
+    assert (cols, rows) == (100, 100)
+    np.testing.assert_array_equal(np.frombuffer(bytes(raw[off:off + 20000]), np.uint16).reshape(100, 100), img)
+
+
+def test_dicom_nesting_depth_is_bounded(host, tmp_path):
+    img = np.zeros((100, 100), np.uint16)
+    path = str(tmp_path / "deep.dcm")
+    err = C.create_string_buffer(256)
+    host.nm03h_dicom_write(path.encode(), img.ctypes.data_as(C.c_void_p), 100, 100, 0, 1, 1, err, 256)
+    raw = bytearray(open(path, "rb").read())
+    pos = raw.find(struct.pack("<HH", 0x7FE0, 0x0010))
+    opener = struct.pack("<HH2sHI", 0x0009, 0x1001, b"SQ", 0, 0xFFFFFFFF) + struct.pack("<HHI", 0xFFFE, 0xE000, 0xFFFFFFFF)
+    raw[pos:pos] = opener * 200
+    open(path, "wb").write(raw)
+    with pytest.raises(RuntimeError, match="nested deeper"):
+        _read(host, path)
+
+
 @pytest.mark.parametrize("channels", [1, 3])
 def test_jpeg_decodes_close_to_source(host, channels):
     from PIL import Image
