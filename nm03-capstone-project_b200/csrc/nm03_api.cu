@@ -54,13 +54,20 @@ const int g_force_cluster = [] { const char* e = getenv("NM03_CLUSTER"); return 
 // thread (lower wake-up latency for a lone caller, one busy core per waiting thread)
 const bool g_spin_wait = [] { const char* e = getenv("NM03_SPIN_WAIT"); return e && e[0] == '1'; }();
 
+// NM03_SPLIT=1: a device-resident batch of a lone single-stream caller is spread over library streams (fork / join on
+// the caller's stream).  Off by default: measured slower than leaving the batch whole (see nm03_process_batch_device).
+const bool g_no_split = [] { const char* e = getenv("NM03_SPLIT"); return !(e && e[0] == '1'); }();
+const int g_split_parts = [] { const char* e = getenv("NM03_SPLIT_PARTS"); const int v = e ? atoi(e) : 0; return v >= 2 && v <= 7 ? v : 4; }();  // tuning
+
 const bool g_force_exact = [] { const char* e = getenv("NM03_FORCE_EXACT_SHARPEN"); return e && e[0] == '1'; }();
 
 struct Slot {
   cudaStream_t stream = nullptr;
   cudaEvent_t done = nullptr;     // recorded after the last use of this slot's scratch
+  cudaEvent_t fork = nullptr;     // recorded on a caller's stream before parts of its batch move to library streams
   std::atomic<bool> used{false};
   std::atomic<cudaStream_t> last_stream{nullptr};  // the stream `done` was last recorded on (both read by other callers' slots)
+  std::atomic<cudaStream_t> forked_from{nullptr};  // caller stream whose batch this slot last carried a part of (null: none)
   uint32_t* pred = nullptr;       // scratch: predicate bit-plane [n][h][wpr]
   size_t pred_bytes = 0;
   void* stage_in = nullptr;       // scratch: device copy of host inputs
@@ -85,8 +92,24 @@ struct ProfRec {
   cudaEvent_t e[3] = {nullptr, nullptr, nullptr};  // before K1, between, after K23
 };
 
+// Everything of a pipeline call that depends only on (parameters, slice size, seed list, which K1 mode): the two kernel
+// parameter blocks with all host-side preparation done (Gaussian masks, error bounds of the fast predicate, clip-floor
+// key, tile order, validated seeds, structuring elements).  A caller repeats the same few combinations for every batch,
+// so they are prepared once and looked up afterwards.
+struct Plan {
+  nm03_params params;
+  int w = 0, h = 0, n_seeds = -1;          // n_seeds = -1: the adaptive seeds
+  std::vector<int> seeds;
+  bool exact = false, erode_out = false;
+  int hs = 0, k1_mode = 0;
+  nm03::PreParams pre;
+  nm03::SegParams seg;
+};
+
 struct Worker {
   int device = 0;
+  std::mutex plan_mu;
+  std::vector<Plan> plans;                 // small most-recently-used list
   Slot slots[kSlots];
   std::atomic<int> host_calls{0};   // nm03_process_batch calls in flight on this GPU
   std::mutex mu;
@@ -164,6 +187,7 @@ bool others_in_flight(Worker* wk, const Slot* mine, cudaStream_t st) {
   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) { (void)cudaGetLastError(); return false; }
   for (auto& o : wk->slots) {
     if (&o == mine || !o.used.load(std::memory_order_relaxed) || o.last_stream.load(std::memory_order_relaxed) == st) continue;
+    if (o.forked_from.load(std::memory_order_relaxed) == st) continue;   // a part of this caller's own previous batch: st waits for it anyway
     if (cudaEventQuery(o.done) == cudaErrorNotReady) {
       (void)cudaGetLastError();   // "not ready" is an answer, not a failure: keep it out of the next launch check
       return true;
@@ -176,6 +200,7 @@ int mark_used(Slot* s, cudaStream_t st) {
   CK(cudaEventRecord(s->done, st));
   s->used = true;
   s->last_stream = st;
+  s->forked_from = nullptr;
   return NM03_OK;
 }
 
@@ -277,6 +302,11 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
       return fail(NM03_ERR_UNSUPPORTED, "zero border mode with uint16 input is not implemented");
     if (f_host(-32768.0f, p) != f_host(-32767.0f, p))
       return fail(NM03_ERR_UNSUPPORTED, "zero border mode needs f(-32768) == f(-32767) for these parameters");
+    // the sentinel sorts below every real key, which is only the position of 0.0 in the window if f() is
+    // non-decreasing in the key and never negative
+    if (!((double)k.norm_scale * (double)k.norm_range > 0.0) || f_host(-32767.0f, p) < 0.0f)
+      return fail(NM03_ERR_UNSUPPORTED, "zero border mode needs a non-decreasing normalisation whose clipped values are >= 0 "
+                  "(clip_min %g, scale %g, range %g)", (double)p->clip_min, (double)k.norm_scale, (double)k.norm_range);
   }
   // normalised Gaussian exactly as FAST's host code builds it: x outer, y inner
   const int m = 2 * sharpen_half + 1;
@@ -413,18 +443,24 @@ int pick_cluster(int n, int h, int wpr, int* rows_per, bool throughput) {
   return c;
 }
 
-int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, const int* seeds_xy, int n_seeds,
-             bool do_fill, bool throughput = false) {
-  memset(&k, 0, sizeof(k));
-  k.w = w; k.h = h; k.n = n; k.wpr = (w + 31) / 32;
+// the batch-dependent part of SegParams: cluster size (or the band height of the fallback) and rows per sweep
+int seg_set_batch(nm03::SegParams& k, int n, bool throughput) {
+  k.n = n;
   int rows = 0;
-  const int c = pick_cluster(n, h, k.wpr, &rows, throughput);
+  const int c = pick_cluster(n, k.h, k.wpr, &rows, throughput);
   if (c < 0) return c;
   k.cluster = c;
   k.rows_per = rows;
   int seg = (rows * k.wpr + nm03::SEG_THREADS - 1) / nm03::SEG_THREADS;
   k.seg_rows = seg < 4 ? 4 : (seg > 16 ? 16 : seg);   // 8-16 rows per sweep measured best (tools/k_time.py)
   if (g_seg_rows > 0) k.seg_rows = g_seg_rows;   // NM03_SEG_ROWS: tuning override
+  return NM03_OK;
+}
+
+// everything of SegParams that does not depend on the batch size
+int fill_seg_static(nm03::SegParams& k, const nm03_params* p, int w, int h, const int* seeds_xy, int n_seeds, bool do_fill) {
+  memset(&k, 0, sizeof(k));
+  k.w = w; k.h = h; k.wpr = (w + 31) / 32;
   k.do_fill = do_fill;
   if (do_fill) {
     if (p->rg_connectivity != 4 && p->rg_connectivity != 8)
@@ -451,6 +487,13 @@ int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, cons
     k.n_seeds = n_seeds;
   }
   return NM03_OK;
+}
+
+int fill_seg(nm03::SegParams& k, const nm03_params* p, int n, int w, int h, const int* seeds_xy, int n_seeds,
+             bool do_fill, bool throughput = false) {
+  int rc;
+  if ((rc = fill_seg_static(k, p, w, h, seeds_xy, n_seeds, do_fill))) return rc;
+  return seg_set_batch(k, n, throughput);
 }
 
 int get_worker(nm03_ctx* ctx, int gpu, Worker** wk) {
@@ -515,19 +558,52 @@ int ensure_lut(Worker* wk, Slot* s, cudaStream_t st, nm03::PreParams& pre) {
 }
 
 // queue K1 + K23 for n device-resident slices on `st`
+// how the segment kernel's cluster size is chosen: for the shortest latency of this batch (wide clusters), for the
+// least interference with other batches (smallest cluster that fits), or by looking at what else is in flight
+enum SegPolicy { SEG_LATENCY = 0, SEG_LOOK = 1, SEG_THROUGHPUT = 2 };
+
 int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h,
-                     const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out, bool resident_caller) {
+                     const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out, SegPolicy policy) {
   int rc, hs = 0;
   if ((rc = check_params(p, w, h, true))) return rc;
-  if ((rc = check_preprocess(p, &hs))) return rc;
+  const bool exact = d_out->sharpened || g_force_exact, erode_out = p->erode_size > 0 && d_out->eroded;
   nm03::PreParams pre;
-  if ((rc = fill_pre(pre, p, n, w, h, hs))) return rc;
   nm03::SegParams seg;
-  if ((rc = fill_seg(seg, p, n, w, h, seeds_xy, n_seeds, true, resident_caller && others_in_flight(wk, s, st)))) return rc;
-  if ((rc = se_halfwidths(p->dilate_size, p->se_shape, &seg.dil_n, seg.dil_hw))) return rc;
-  if (p->erode_size > 0 && d_out->eroded) {
-    if ((rc = se_halfwidths(p->erode_size, p->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
+  int k1_mode = nm03::K1_EXACT;
+  bool hit = false;
+  {
+    std::lock_guard<std::mutex> lk(wk->plan_mu);
+    for (size_t i = 0; i < wk->plans.size(); ++i) {
+      Plan& c = wk->plans[i];
+      if (c.w != w || c.h != h || c.exact != exact || c.erode_out != erode_out || memcmp(&c.params, p, sizeof(*p)) != 0) continue;
+      if (seeds_xy ? (c.n_seeds != n_seeds || (n_seeds > 0 && memcmp(c.seeds.data(), seeds_xy, sizeof(int) * 2 * n_seeds) != 0)) : c.n_seeds != -1) continue;
+      pre = c.pre; seg = c.seg; hs = c.hs; k1_mode = c.k1_mode;
+      if (i != 0) std::swap(wk->plans[0], wk->plans[i]);
+      hit = true;
+      break;
+    }
   }
+  if (!hit) {
+    if ((rc = check_preprocess(p, &hs))) return rc;
+    if ((rc = fill_pre(pre, p, 0, w, h, hs))) return rc;
+    if ((rc = fill_seg_static(seg, p, w, h, seeds_xy, n_seeds, true))) return rc;
+    if ((rc = se_halfwidths(p->dilate_size, p->se_shape, &seg.dil_n, seg.dil_hw))) return rc;
+    if (erode_out) {
+      if ((rc = se_halfwidths(p->erode_size, p->se_shape, &seg.ero_n, seg.ero_hw))) return rc;
+    }
+    k1_mode = exact ? nm03::K1_EXACT : fill_fast(pre, p, hs);
+    Plan c;
+    c.params = *p; c.w = w; c.h = h; c.exact = exact; c.erode_out = erode_out; c.hs = hs; c.k1_mode = k1_mode;
+    c.n_seeds = seeds_xy ? n_seeds : -1;
+    if (seeds_xy && n_seeds > 0) c.seeds.assign(seeds_xy, seeds_xy + 2 * n_seeds);
+    c.pre = pre; c.seg = seg;
+    std::lock_guard<std::mutex> lk(wk->plan_mu);
+    wk->plans.insert(wk->plans.begin(), std::move(c));
+    if (wk->plans.size() > 8) wk->plans.pop_back();
+  }
+  pre.n = n;
+  const bool throughput = policy == SEG_THROUGHPUT || (policy == SEG_LOOK && others_in_flight(wk, s, st));
+  if ((rc = seg_set_batch(seg, n, throughput))) return rc;
   const size_t pred_bytes = (size_t)n * h * pre.wpr * 4;
   if ((rc = ensure(s, (void**)&s->pred, &s->pred_bytes, pred_bytes))) return rc;
   if ((rc = order_after_last_use(s, st))) return rc;
@@ -541,7 +617,6 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   pre.median = d_out->median;
   pre.sharpened = d_out->sharpened;
   pre.predicate = s->pred;
-  const int k1_mode = (d_out->sharpened || g_force_exact) ? nm03::K1_EXACT : fill_fast(pre, p, hs);
   ProfRec rec;
   const bool prof = wk->profiling.load() != 0;
   if (prof) {
@@ -729,6 +804,7 @@ int nm03_init(const int* gpu_ids, int n_gpus, nm03_ctx** out) {
     for (auto& s : wk->slots) {
       if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
       if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming | (g_spin_wait ? 0 : cudaEventBlockingSync));
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming);
     }
     if (e != cudaSuccess) {
       nm03_shutdown(ctx);
@@ -757,6 +833,7 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.dflag) cudaFree(s.dflag);
       if (s.hflag) cudaFreeHost(s.hflag);
       if (s.done) cudaEventDestroy(s.done);
+      if (s.fork) cudaEventDestroy(s.fork);
       if (s.stream) cudaStreamDestroy(s.stream);
     }
     delete wk;
@@ -849,7 +926,66 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
   DeviceGuard g(wk->device);
   SlotLease lease(wk, (cudaStream_t)stream);
   cudaStream_t st = stream ? (cudaStream_t)stream : lease.s->stream;
-  return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out, true);
+  // A caller that keeps several streams busy gets its batches overlapped by the GPU: the latency-bound fill of one runs
+  // under the ALU-bound preprocess kernel of the next.  Opt-in experiment (NM03_SPLIT=1) for a caller with ONE stream:
+  // when nothing else is in flight the batch is cut into parts, part 0 stays on the caller's stream, the others go to
+  // library streams behind an event of the caller's stream (fork), and the caller's stream waits for their events
+  // (join); everything is still complete where the caller's stream says it is.  Measured on B200, 24 slices 512x512
+  // back to back on one stream: 79.5 us whole, 95 / 103 / 105 us in 2 / 3 / 4 parts (96 slices: 215 us whole,
+  // 213 / 225 / 234 us in 2 / 4 / 6 parts) — stream order forces every call to end with an exposed fill of its last
+  // part, the parts' fills run with the small clusters, and the events cost more than the overlap returns.  Hence off.
+  int parts = 1;
+  if (!g_no_split && n >= 12 && wk->profiling.load() == 0 && !others_in_flight(wk, lease.s, st)) {
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) parts = n / 6 < g_split_parts ? n / 6 : g_split_parts;
+    else (void)cudaGetLastError();
+  }
+  if (parts <= 1) return enqueue_pipeline(wk, lease.s, st, d_slices, n, w, h, params, seeds_xy, n_seeds, d_out, SEG_LOOK);
+  if ((rc = check_params(params, w, h, true))) return rc;
+  const size_t npx = (size_t)w * h, wpr = (size_t)(w + 31) / 32;
+  CK(cudaEventRecord(lease.s->fork, st));
+  // the slots of the parts are held until all parts are queued: a slot handed back early would be the next part's pick,
+  // and the parts would line up on one stream
+  struct Held {
+    Worker* wk;
+    std::vector<Slot*> v;
+    ~Held() { for (Slot* s : v) release(wk, s); }
+  } held{wk, {}};
+  int start = 0;
+  for (int i = 0; i < parts && start < n; ++i) {
+    int cnt = (n - start) / (parts - i);
+    Slot* s = lease.s;
+    if (i > 0) {
+      s = acquire(wk, false);
+      if (!s) { s = lease.s; cnt = n - start; }          // no free slot: the rest follows part 0 on the caller's stream
+      else held.v.push_back(s);
+    }
+    cudaStream_t ss = (s == lease.s) ? st : s->stream;
+    nm03_outputs o = *d_out;
+    if (o.dilated) o.dilated += start * npx;
+    if (o.eroded) o.eroded += start * npx;
+    if (o.rg_mask) o.rg_mask += start * npx;
+    if (o.sharpened) o.sharpened += start * npx;
+    if (o.median) o.median += start * npx;
+    if (o.rg_iterations) o.rg_iterations += start;
+    if (o.dilated_bits) o.dilated_bits += start * h * wpr;
+    rc = NM03_OK;
+    if (ss != st) {
+      cudaError_t e = cudaStreamWaitEvent(ss, lease.s->fork, 0);
+      if (e != cudaSuccess) rc = fail(NM03_ERR_CUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString(e));
+    }
+    const bool last = start + cnt >= n;
+    if (!rc) rc = enqueue_pipeline(wk, s, ss, (const uint8_t*)d_slices + start * npx * 2, cnt, w, h, params, seeds_xy, n_seeds, &o,
+                                   last ? SEG_LATENCY : SEG_THROUGHPUT);
+    if (!rc && ss != st) {
+      s->forked_from = st;
+      cudaError_t e = cudaStreamWaitEvent(st, s->done, 0);   // join: recorded by enqueue_pipeline behind the part's last kernel
+      if (e != cudaSuccess) rc = fail(NM03_ERR_CUDA, "cudaStreamWaitEvent failed: %s", cudaGetErrorString(e));
+    }
+    if (rc) return rc;
+    start += cnt;
+  }
+  return NM03_OK;
 }
 
 // One chunk [start, start+cnt) of a host-buffer batch on slot s: H2D copy, K1 + K23, D2H copies of every requested
@@ -889,7 +1025,7 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
   if (out->dilated_bits) d.dilated_bits = (uint32_t*)(so + o_bits);
   if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
   // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
-  if ((rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, false))) return rc;
+  if ((rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, SEG_LATENCY))) return rc;
 #define NM03_D2H(field, off, elem)                                                                          \
   if (out->field && e == cudaSuccess)                                                                       \
     e = cudaMemcpyAsync((uint8_t*)out->field + (size_t)start * npx * (elem), so + (off), cnt * npx * (elem), \

@@ -624,6 +624,9 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // ---- phase C: unsharp mask, range predicate, stores ------------------------------------------
   const int lane = tid & 31;
   if (MODE == K1_EXACT) {
+  // 16-byte stores of the float planes need rows that start on 16 bytes: a width that is a multiple of 4 AND base
+  // pointers aligned to 16 bytes (a device-entry caller may pass a view at any 4-byte offset)
+  const bool vec4 = (w & 3) == 0 && (((uintptr_t)p.sharpened | (uintptr_t)p.median) & 15) == 0;
   // every pixel in the oracle's exact operation order (one warp = one 128-pixel output row)
   for (int it = tid; it < K1_TH * (K1_TW / 4); it += K1_THREADS) {
     const int oyl = it / (K1_TW / 4), xq = it - oyl * (K1_TW / 4);
@@ -645,13 +648,13 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     }
     const size_t rowoff = ((size_t)slice * h + oy) * w;
     if (p.sharpened) {
-      if ((w & 3) == 0 && ox + 3 < w) *reinterpret_cast<float4*>(p.sharpened + rowoff + ox) = make_float4(sv[0], sv[1], sv[2], sv[3]);
+      if (vec4 && ox + 3 < w) *reinterpret_cast<float4*>(p.sharpened + rowoff + ox) = make_float4(sv[0], sv[1], sv[2], sv[3]);
       else
 #pragma unroll
         for (int j = 0; j < 4; ++j) if (ox + j < w) p.sharpened[rowoff + ox + j] = sv[j];
     }
     if (p.median) {
-      if ((w & 3) == 0 && ox + 3 < w) *reinterpret_cast<float4*>(p.median + rowoff + ox) = c4;
+      if (vec4 && ox + 3 < w) *reinterpret_cast<float4*>(p.median + rowoff + ox) = c4;
       else
 #pragma unroll
         for (int j = 0; j < 4; ++j) if (ox + j < w) p.median[rowoff + ox + j] = cv[j];

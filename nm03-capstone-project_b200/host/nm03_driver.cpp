@@ -42,6 +42,7 @@ struct Options {
   std::vector<int> gpus;
   int batch = 25, streams = 3, host_threads = 0;   // 3 feeders per GPU measured best (21-29k slices/s from files in /dev/shm)
   bool do_export = true, dump_masks = false, lowcontrast = false;
+  bool byte_masks = false;   // --byte-masks: fetch the uint8 mask from the GPU instead of the bit-packed one (8x the bytes over the link)
   int patients = 20, slices = 24, size = 512;
 };
 
@@ -156,6 +157,29 @@ struct Pinned {
   ~Pinned() { if (p) nm03_host_free(p); }
 };
 
+// bit-packed mask row-words -> uint8 {0,1} pixels (nm03_outputs.dilated_bits; bit x%32 of word x/32 = pixel x)
+void unpackMask(const uint32_t* bits, int w, int h, uint8_t* out) {
+  static const auto table = [] {
+    std::vector<uint64_t> t(256);
+    for (int b = 0; b < 256; ++b) { uint64_t v = 0; for (int i = 0; i < 8; ++i) v |= (uint64_t)((b >> i) & 1) << (8 * i); t[b] = v; }
+    return t;
+  }();
+  const int wpr = (w + 31) / 32;
+  for (int y = 0; y < h; ++y) {
+    const uint32_t* row = bits + (size_t)y * wpr;
+    uint8_t* o = out + (size_t)y * w;
+    int x = 0;
+    for (int k = 0; k < wpr; ++k) {
+      const uint32_t word = row[k];
+      for (int byte = 0; byte < 4 && x < w; ++byte, x += 8) {
+        const uint64_t v = table[(word >> (8 * byte)) & 0xffu];
+        if (x + 8 <= w) std::memcpy(o + x, &v, 8);
+        else std::memcpy(o + x, &v, (size_t)(w - x));
+      }
+    }
+  }
+}
+
 void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const uint8_t* mask, int w, int h) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
@@ -229,7 +253,6 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     const int w = slices[first].cols, h = slices[first].rows, m = (int)idx.size();
     const size_t npx = (size_t)w * h;
     in.reserve(m * npx * 2);
-    out.reserve(m * npx);
     std::atomic<int> read_failed{0};
     parallel_for(m, opt.host_threads, [&](int j) {
       try {
@@ -247,8 +270,12 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     timer.lap(tot.ns_read);
     params.input_unsigned = nm03::dicom::rescaled_representation(slices[first].pixel_representation, slices[first].rescale_slope,
                                                                  slices[first].rescale_intercept) == 0;
+    // the mask comes back bit-packed (1/8 of the bytes over the host link) and is unpacked by the worker that needs it
+    const size_t wpr = (size_t)(w + 31) / 32, mask_bytes = opt.byte_masks ? npx : h * wpr * 4;
+    out.reserve(m * mask_bytes);
     nm03_outputs o = {};
-    o.dilated = (uint8_t*)out.p;
+    if (opt.byte_masks) o.dilated = (uint8_t*)out.p;
+    else o.dilated_bits = (uint32_t*)out.p;
     std::vector<int> status(m, 0);
     const int rc = nm03_process_batch(ctx, gpu, in.p, m, w, h, &params, nullptr, 0, &o, status.data());
     timer.lap(tot.ns_gpu);
@@ -259,16 +286,25 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       continue;  // a failed group is skipped, the patient goes on (main_parallel.cpp:163-167)
     }
     ok += m;
+    auto mask_of = [&](int j, std::vector<uint8_t>& scratch) -> const uint8_t* {
+      if (opt.byte_masks) return (const uint8_t*)out.p + j * npx;
+      scratch.resize(npx);
+      unpackMask((const uint32_t*)((const uint8_t*)out.p + j * mask_bytes), w, h, scratch.data());
+      return scratch.data();
+    };
     if (opt.dump_masks)
       for (int j = 0; j < m; ++j) {
+        std::vector<uint8_t> scratch;
+        const uint8_t* mk = mask_of(j, scratch);
         FILE* f = std::fopen((outdir / (fs::path(files[idx[j]]).stem().string() + ".mask")).string().c_str(), "wb");
-        if (f) { std::fwrite((uint8_t*)out.p + j * npx, 1, npx, f); std::fclose(f); }
+        if (f) { std::fwrite(mk, 1, npx, f); std::fclose(f); }
       }
     if (opt.do_export)
       parallel_for(m, opt.host_threads, [&](int j) {
         try {
+          thread_local std::vector<uint8_t> scratch;
           exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
-                      (uint8_t*)out.p + j * npx, w, h);
+                      mask_of(j, scratch), w, h);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(tot.log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -422,7 +458,8 @@ int runTestPipeline(const Options& opt) {
 }
 
 int makeDataset(const Options& opt) {
-  for (int p = 0; p < opt.patients; ++p) {
+  Pool pool(std::max(0, opt.host_threads - 1));
+  pool.parallel_for(opt.patients, [&](int p) {
     char name[64];
     std::snprintf(name, sizeof(name), "PGBM-%03d", p + 1);
     const fs::path dir = fs::path(opt.make_dataset) / name / "01-01-2000-synthetic" ;
@@ -433,7 +470,7 @@ int makeDataset(const Options& opt) {
       std::snprintf(fn, sizeof(fn), "1-%02d.dcm", s + 1);
       nm03::dicom::save((dir / fn).string(), (const uint16_t*)px.data(), opt.size, opt.size, true, s + 1, (p & 1) == 0);
     }
-  }
+  });
   std::cout << "wrote " << opt.patients << " patients x " << opt.slices << " slices " << opt.size << "x" << opt.size << " under "
             << opt.make_dataset << std::endl;
   return 0;
@@ -456,6 +493,7 @@ int main(int argc, char** argv) {
     else if (a == "--host-threads") opt.host_threads = std::atoi(val().c_str());
     else if (a == "--no-export") opt.do_export = false;
     else if (a == "--dump-masks") opt.dump_masks = true;
+    else if (a == "--byte-masks") opt.byte_masks = true;
     else if (a == "--test-pipeline") opt.test_file = val();
     else if (a == "--make-dataset") opt.make_dataset = val();
     else if (a == "--patients") opt.patients = std::atoi(val().c_str());

@@ -7,6 +7,7 @@ import subprocess
 import sys
 import textwrap
 
+import numpy as np
 import pytest
 
 import common as cm
@@ -58,3 +59,43 @@ def test_variant_matches_oracle(name):
     env = dict(os.environ, **VARIANTS[name])
     r = subprocess.run([sys.executable, "-c", CODE], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "variant ok" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_zero_border_with_negative_values_is_refused_not_wrong(lib):
+    """The zero-border mode carries out-of-image samples as the lowest key, which is only the place of 0.0 in a sorted
+    window when clip(normalise()) is non-decreasing and never negative; other parameter sets are refused."""
+    raw = cm.phantom(128, 128, 1, 1)
+    with lib.Context([0]) as ctx:
+        for kw in (dict(clip_min=-3.0, norm_low=-1.0), dict(norm_low=2.5, norm_high=0.5)):
+            with pytest.raises(lib.Nm03Error) as e:
+                ctx.preprocess(raw, lib.default_params(border_mode=1, **kw))
+            assert e.value.code == lib.ERR_UNSUPPORTED and "zero border" in str(e.value)
+        got = ctx.preprocess(raw, lib.default_params(border_mode=1, clip_min=0.0))      # 0.0 itself is fine
+    f = cm.o_clip(cm.o_normalize(raw), 0.0, 4000.0)
+    np.testing.assert_array_equal(got["median"], cm.o_median(f, 7, 1))
+
+
+def test_device_entry_accepts_float_planes_at_any_4_byte_offset(lib):
+    """A caller may hand in a view into a larger buffer: the float outputs then start on a 4-byte, not a 16-byte, boundary."""
+    import torch
+    raw = np.stack([cm.phantom(256, 256, 6, s) for s in range(2)])
+    with lib.Context([0]) as ctx:
+        d_in = torch.from_numpy(raw).cuda()
+        n = raw.size
+        flat_s = torch.zeros(n + 8, dtype=torch.float32, device="cuda")
+        flat_m = torch.zeros(n + 8, dtype=torch.float32, device="cuda")
+        d_mask = torch.zeros(raw.shape, dtype=torch.uint8, device="cuda")
+        res = {}
+        for off in (0, 1, 3):
+            o = lib.Outputs()
+            o.sharpened = flat_s.data_ptr() + 4 * off
+            o.median = flat_m.data_ptr() + 4 * off
+            o.dilated = d_mask.data_ptr()
+            ctx.process_batch_device(d_in.data_ptr(), 2, 256, 256, lib.default_params(), o)
+            torch.cuda.synchronize()
+            res[off] = (flat_s[off:off + n].cpu().numpy().copy(), flat_m[off:off + n].cpu().numpy().copy())
+    rc, exp = cm.o_pipeline(raw[0])
+    np.testing.assert_array_equal(res[0][0][:256 * 256].reshape(256, 256), exp["sharpened"])
+    for off in (1, 3):
+        np.testing.assert_array_equal(res[off][0], res[0][0])
+        np.testing.assert_array_equal(res[off][1], res[0][1])

@@ -250,14 +250,38 @@ def test_pipeline_ragged_and_switches(lib, ctx):
 
 
 def test_pipeline_median_window_9_and_unsupported_windows(lib, ctx):
-    """N4 generality: 9x9 is implemented (slower network); larger odd windows are refused, even ones are
+    """N4 generality: 9x9 is implemented (slower network); windows above 15 are refused, even ones are
     a parameter error as in FAST."""
     raws = np.stack([cm.phantom(300, 260, 9, i) for i in range(2)])
     _cmp_pipeline(lib, ctx, raws, median_window=9, dilate_size=5)
-    for k, code in ((11, lib.ERR_UNSUPPORTED), (4, lib.ERR_PARAM)):
+    for k, code in ((17, lib.ERR_UNSUPPORTED), (4, lib.ERR_PARAM), (1, lib.ERR_PARAM)):
         with pytest.raises(lib.Nm03Error) as e:
             ctx.process_batch(raws, lib.default_params(median_window=k))
         assert e.value.code == code
+
+
+# ---- median windows 11, 13, 15: the generic rank search (no generated network) ---------------------
+@pytest.mark.parametrize("k", [11, 13, 15])
+@pytest.mark.parametrize("m", [3, 9])
+def test_preprocess_large_windows(lib, ctx, k, m):
+    _cmp_pre(lib, ctx, cm.phantom(160, 110, 2, k + m), median_window=k, sharpen_mask=m, sharpen_sigma=0.8)
+
+
+@pytest.mark.parametrize("k", [11, 15])
+def test_preprocess_large_windows_value_ranges_and_borders(lib, ctx, k):
+    rng = np.random.default_rng(k)
+    _cmp_pre(lib, ctx, rng.integers(-32768, 32768, (140, 133)).astype(np.int16), median_window=k)   # all 16 bits in play
+    _cmp_pre(lib, ctx, rng.integers(0, 65536, (128, 160)).astype(np.uint16), median_window=k)
+    _cmp_pre(lib, ctx, rng.integers(1195, 1206, (140, 133)).astype(np.int16), median_window=k)      # heavy ties
+    _cmp_pre(lib, ctx, np.full((120, 120), 1200, np.int16), median_window=k)                         # one value only
+    _cmp_pre(lib, ctx, cm.phantom(200, 150, 4, 1), median_window=k, border_mode=1)                   # zero border sentinel
+    _cmp_pre(lib, ctx, cm.phantom(517, 203, 4, 2), median_window=k)                                  # no TMA (width % 8), ragged tiles
+    _cmp_fast(lib, ctx, cm.phantom(256, 256, 2, 5), median_window=k)                                 # fast predicate mode
+
+
+def test_pipeline_median_window_13(lib, ctx):
+    raws = np.stack([cm.phantom(512, 512, 9, i) for i in range(3)])
+    _cmp_pipeline(lib, ctx, raws, median_window=13, dilate_size=5, erode_size=3)
 
 
 def test_pipeline_dimension_guard(lib, ctx):

@@ -222,3 +222,70 @@ def test_batch_omp_matches_single():
     assert ok == 5
     for i in range(5):
         np.testing.assert_array_equal(out[i], cm.o_pipeline(raws[i])[1]["dilated"])
+
+
+# ---- hand-derived vectors: worked out on paper from SURVEY §8c, not produced by the oracle or by scipy ---------
+def test_hand_vector_median_3x3_corners():
+    img = np.arange(1, 10, dtype=np.float32).reshape(3, 3)          # 1 2 3 / 4 5 6 / 7 8 9
+    # clamp-to-edge, corner (0,0): rows {0,0,1} x cols {0,0,1} -> 1 1 2 | 1 1 2 | 4 4 5 -> sorted 1 1 1 1 [2] 2 4 4 5
+    # corner (2,2): 5 6 6 | 8 9 9 | 8 9 9 -> sorted 5 6 6 8 [8] 9 9 9 9;  edge (0,1): 1 2 3 | 1 2 3 | 4 5 6 -> 1 1 2 2 [3] 3 4 5 6
+    clamp = cm.o_median(img, 3, 0)
+    assert clamp[0, 0] == 2 and clamp[2, 2] == 8 and clamp[0, 1] == 3 and clamp[1, 1] == 5
+    # zero border, corner (0,0): 0 0 0 | 0 1 2 | 0 4 5 -> 0 0 0 0 [0] 1 2 4 5;  corner (2,2): 5 6 0 | 8 9 0 | 0 0 0 -> 0 0 0 0 [0] 5 6 8 9
+    # edge (1,0): 0 1 2 | 0 4 5 | 0 7 8 -> 0 0 0 1 [2] 4 5 7 8
+    zero = cm.o_median(img, 3, 1)
+    assert zero[0, 0] == 0 and zero[2, 2] == 0 and zero[1, 0] == 2 and zero[1, 1] == 5
+
+
+def test_hand_vector_region_growing_5x5():
+    v = np.array([[1, 1, 0, 1, 1],
+                  [0, 1, 0, 0, 1],
+                  [0, 1, 1, 0, 0],
+                  [0, 0, 1, 0, 1],
+                  [1, 0, 0, 1, 1]], np.float32) * 0.8        # 0.8 is inside [0.74, 0.91], 0 is not
+    # 4-connectivity from (x=1, y=1): (1,1) (0,0) (1,0) (1,2) (2,2) (2,3) and nothing else; the diagonal neighbours
+    # (3,4)/(4,4)/(4,3) are only reached with 8-connectivity, the top-right block and (0,4) never
+    exp4 = np.array([[1, 1, 0, 0, 0],
+                     [0, 1, 0, 0, 0],
+                     [0, 1, 1, 0, 0],
+                     [0, 0, 1, 0, 0],
+                     [0, 0, 0, 0, 0]], np.uint8)
+    exp8 = exp4.copy()
+    exp8[4, 3] = exp8[4, 4] = exp8[3, 4] = 1
+    rc, m4, _ = cm.o_region_grow(v, 0.74, 0.91, [(1, 1)], conn=4)
+    assert rc == 0
+    np.testing.assert_array_equal(m4, exp4)
+    rc, m8, _ = cm.o_region_grow(v, 0.74, 0.91, [(1, 1)], conn=8)
+    np.testing.assert_array_equal(m8, exp8)
+    # a seed on an out-of-range pixel grows nothing in the OpenCL mode; two seeds give the union of their components
+    rc, m0, _ = cm.o_region_grow(v, 0.74, 0.91, [(2, 0)], conn=4)
+    assert rc == 0 and m0.sum() == 0
+    rc, mu, _ = cm.o_region_grow(v, 0.74, 0.91, [(1, 1), (4, 0)], conn=4)
+    expu = exp4.copy()
+    expu[0, 3] = expu[0, 4] = expu[1, 4] = 1
+    np.testing.assert_array_equal(mu, expu)
+    # host mode: the seed pixel is only labelled when reached from a neighbour — an isolated in-range seed stays 0
+    rc, mh, _ = cm.o_region_grow(v, 0.74, 0.91, [(0, 4)], mode=1, conn=4)
+    assert rc == 0 and mh.sum() == 0
+
+
+def test_hand_vector_single_pixel_morphology():
+    m = np.zeros((7, 7), np.uint8)
+    m[3, 3] = 1
+    plus = np.zeros((7, 7), np.uint8)
+    plus[3, 2:5] = 1
+    plus[2:5, 3] = 1                                           # size 3 -> N = 1 -> disc a^2+b^2 <= 1: the 5-pixel plus
+    rc, d = cm.o_dilate(m, 3, 0)
+    np.testing.assert_array_equal(d, plus)
+    rc, d = cm.o_dilate(m, 3, 1)                               # square SE: the full 3x3 block
+    assert d.sum() == 9 and d[2:5, 2:5].all()
+    rc, e = cm.o_erode(plus, 3, 0)                             # the plus eroded by the plus: only its centre survives
+    np.testing.assert_array_equal(e, m)
+    rc, e = cm.o_erode(plus, 3, 1)
+    assert e.sum() == 0                                        # no 3x3 block fits into a plus
+    corner = np.zeros((5, 5), np.uint8)
+    corner[0:2, 0:2] = 1
+    rc, e = cm.o_erode(corner, 3, 0)
+    assert e.sum() == 0                                        # outside the image counts as 0: border pixels never survive
+    rc, d5 = cm.o_dilate(m, 5, 0)                              # N = 2: 13 pixels (rows of 1, 3, 5, 3, 1)
+    assert d5.sum() == 13 and [int(r.sum()) for r in d5[1:6]] == [1, 3, 5, 3, 1]

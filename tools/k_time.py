@@ -17,7 +17,7 @@ n_batches = flat.shape[0] // n
 d_out = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
 o = nm03.Outputs(); o.dilated = d_out.data_ptr()
 it = torch.zeros(n, dtype=torch.int32, device=dev); o.rg_iterations = it.data_ptr()
-params = nm03.default_params()
+params = nm03.default_params(median_window=int(os.environ.get('K_TIME_WINDOW', '7')))
 st = torch.cuda.Stream(device=dev)
 for i in range(5):
     ctx.process_batch_device(flat[(i % n_batches) * n:].data_ptr(), n, W, H, params, o, st.cuda_stream)

@@ -76,7 +76,7 @@ if __name__ == "__main__":
     else:
         gpus = [int(x) for x in sys.argv[1].split(",")]
         bind = len(sys.argv) > 2 and sys.argv[2] == "bind"
-        deadline = time.time() + 25.0
+        deadline = time.time() + 15.0
         ps = [subprocess.Popen([sys.executable, __file__, "--child", str(g), "1" if bind else "0", str(deadline)])
               for g in gpus]
         for p in ps:

@@ -1,19 +1,26 @@
 #!/bin/bash
-# Run on a multi-GPU box: topology, concurrent PCIe figures with and without NUMA binding, bench e2e both ways.
-N=${1:-4}
+# Run on a multi-GPU box: topology, host CPUs, concurrent pinned-copy bandwidth with 1 GPU and with all N copying, the
+# bench line at N GPUs (c2 with the DICOM->JPEG driver figure, c3 without), and the driver's per-phase host times.
+N=${1:-8}
 OUT=gpurun_out/multi_probe_$N
 mkdir -p $OUT
 nvidia-smi topo -m > $OUT/topo.txt 2>&1
-(nproc; lscpu | grep -i -E "numa|socket|model name|^CPU\(s\)"; cat /sys/fs/cgroup/cpu.max 2>/dev/null) > $OUT/cpu.txt 2>&1
+(nproc; lscpu | grep -i -E "numa|socket|model name|^CPU\(s\)"; cat /sys/fs/cgroup/cpu.max 2>/dev/null; free -g | head -2) > $OUT/cpu.txt 2>&1
 IDS=$(seq -s, 0 $((N-1)))
-for set in 0 0,1 $IDS; do
-  for b in nobind bind; do
-    echo "== gpus $set $b" >> $OUT/pcie.txt
-    timeout 120 python tools/multi_gpu_pcie_probe.py $set $b >> $OUT/pcie.txt 2>&1
+for set in 0 $IDS; do
+  echo "== gpus $set" >> $OUT/pcie.txt
+  timeout 120 python tools/multi_gpu_pcie_probe.py $set >> $OUT/pcie.txt 2>&1
+done
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 \
+  bench.py --gpus $N --steps 1000 --warmup 10 --cpu-seconds 5 > $OUT/bench_c2.json 2> $OUT/bench_c2.err
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29518 \
+  bench.py --gpus $N --config c3 --steps 50 --warmup 5 --cpu-seconds 1 --no-io > $OUT/bench_c3.json 2> $OUT/bench_c3.err
+D=/dev/shm/nm03_probe
+./nm03-capstone-project_b200/host/nm03_driver --make-dataset $D/d --patients 120 --slices 24 --size 512 > /dev/null
+for extra in "--no-export" ""; do
+  for s in 3 2; do
+    NM03_DRIVER_TIMING=1 ./nm03-capstone-project_b200/host/nm03_driver --data $D/d --out $D/o --gpus $IDS --streams $s $extra 2>> $OUT/driver.txt | tail -1 >> $OUT/driver.txt
   done
 done
-for numa in 0 1; do
-  NM03_BENCH_NUMA=$numa timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 \
-    --master-port 29517 bench.py --gpus $N --steps 300 --warmup 5 --cpu-seconds 2 > $OUT/bench_numa$numa.json 2> $OUT/bench_numa$numa.err
-done
-tail -c 600 $OUT/pcie.txt
+rm -rf $D
+tail -c 1200 $OUT/pcie.txt; cat $OUT/driver.txt; cut -c1-600 $OUT/bench_c2.json; tail -3 $OUT/bench_c2.err
