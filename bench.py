@@ -241,7 +241,7 @@ class ClockSampler:
 def kernel_sources_sha():
     """Hash of the CUDA sources the kernels are built from: an ncu summary is only quoted when it was captured from these."""
     hsh = hashlib.sha256()
-    for name in ("nm03_kernels.cu", "nm03_device.h", "median_net.inc"):
+    for name in ("nm03_kernels.cu", "nm03_k1.cuh", "nm03_k1_w.cu", "nm03_device.h", "median_net.inc"):
         with open(os.path.join(ROOT, PKG, "csrc", name), "rb") as f:
             hsh.update(f.read())
     return hsh.hexdigest()[:16]

@@ -320,7 +320,8 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   for (int i = 0; i < m * m; ++i) k.mask[i] /= sum;
   for (int i = m * m; i < 81; ++i) k.mask[i] = 0.0f;
   for (int i = 0; i < 9; ++i) k.gx[i] = 0.0f;
-  k.ea = k.eb = k.ec = k.eps_max = 0.0f;
+  k.ea = k.eb = k.ec = k.eps_max = k.ean = k.gain1 = 0.0f;
+  for (int i = 0; i < 9; ++i) k.gyn[i] = 0.0f;
   return NM03_OK;
 }
 
@@ -367,7 +368,8 @@ int fill_fast(nm03::PreParams& k, const nm03_params* p, int sharpen_half) {
         }
       }
     const double gM = gamma(m * m), g2 = gamma(2.0 * (2 * he + 1));
-    double c1 = gM + g2 * (1.0 + rho) + rho;
+    // (+ 2u: the kernel's vertical taps are fl(-gain * gx), one more rounding per tap than the analysis above assumes)
+    double c1 = gM + g2 * (1.0 + rho) + rho + 2.0 * u;
     const double c2 = ((1.0 + gM) * d_out + d_abs) * vmax * 1.05;
     double ea, ec = gain * c2;
     if (nonneg) { c1 *= (1.0 + 2.0 * rho + 4.0 * g2) * 1.05; ea = gain * c1 + 6.3 * u * gain; }
@@ -388,6 +390,13 @@ int fill_fast(nm03::PreParams& k, const nm03_params* p, int sharpen_half) {
     k.ea = (float)(ea2 * 1.02) + 1e-12f;
     k.eb = (float)(eb2 * 1.02) + 1e-12f;
     k.ec = (float)(ec2 * 1.02) + 1e-12f;
+    // The kernel forms the sharpened value as fma(fl(1+gain), v, nb) with nb = -gain*blur_a from the scaled taps: two
+    // roundings (the constant, the result) instead of the three of sub/mul/add; both are below the 6.3u|gain|(|v|+|blur|)
+    // + 2.1u|v| already in ea/eb (|1+gain||v| + |s| <= 2(1+|gain|)|v| + |gain||blur|).
+    for (int x = 0; x < 9; ++x) k.gyn[x] = -p->sharpen_gain * k.gx[x];
+    k.gain1 = 1.0f + p->sharpen_gain;
+    k.ean = gain > 0.0 ? (float)((double)k.ea / gain * (1.0 + 4.0 * u)) + 1e-12f : 0.0f;
+    if (!std::isfinite(k.gain1) || !std::isfinite(k.ean)) return nm03::K1_EXACT;
     // widest band of any pixel: |v| <= vmax and |blur_a| <= (sum |gx|)^2 * vmax (inflated for the rounding of the FMAs)
     double gsum = 0.0;
     for (int x = -he; x <= he; ++x) gsum += std::fabs((double)k.gx[x + nm03::K1_HS_MAX]);

@@ -18,15 +18,19 @@ namespace nm03 {
 #ifndef NM03_K1_MIN_CTAS
 #define NM03_K1_MIN_CTAS 2
 #endif
-constexpr int K1_TW = 128;
+#ifndef NM03_K1_TW
+#define NM03_K1_TW 128
+#endif
+constexpr int K1_TW = NM03_K1_TW;                  // multiple of 32 (one predicate word = 32 pixels)
 constexpr int K1_TH = NM03_K1_TH;
 constexpr int K1_HS_MAX = 4;                      // sharpen mask up to 9x9
 constexpr int K1_MW = K1_TW + 2 * K1_HS_MAX;      // 136 median columns
 constexpr int K1_MH = K1_TH + 2 * K1_HS_MAX;      // 72 median rows
 constexpr int K1_MHP = K1_MH / 2;                 // 36 packed median rows (row p and row p+36 share a register)
-constexpr int K1_PWS = 144;                       // packed raw tile row stride in words (>= 136 + 6, multiple of 4)
+constexpr int K1_PWS = K1_MW + 8;                 // packed raw tile row stride in words (>= MW + 2R + OFF for R <= 4, multiple of 8)
+static_assert(K1_TW % 32 == 0 && K1_TH % 8 == 0, "tile shape");
 // windows above 9x9 need a wider halo: their packed tile has a longer row and their TMA box starts further left
-__host__ __device__ constexpr int k1_pws(int K) { return K <= 9 ? K1_PWS : 160; }
+__host__ __device__ constexpr int k1_pws(int K) { return K <= 9 ? K1_PWS : K1_MW + 24; }
 __host__ __device__ constexpr int k1_xbox(int K) { return K <= 9 ? 8 : 16; }
 constexpr int K1_THREADS = NM03_K1_THREADS;
 constexpr int K1_MIN_CTAS = NM03_K1_MIN_CTAS;                   // resident CTAs per SM the register budget is set for
@@ -62,6 +66,9 @@ struct PreParams {
   float gx[9];
   float ea, eb, ec;
   float eps_max;                 // upper bound of eps over every |blur|, |v| these parameters can produce
+  float gyn[9];                  // vertical taps of the fast path scaled by -gain: fl(-gain * gx[t])
+  float gain1;                   // fl(1 + gain)
+  float ean;                     // ea / |gain|: the band in terms of |gain * blur| (what the fast path holds)
   float rg_mid, rg_half;         // fast predicate: inside [rg_min, rg_max]  <=>  |s - rg_mid| - rg_half <= 0 (up to the band)
 };
 

@@ -14,6 +14,8 @@
 // per-patient success counts (:286-299).  Not kept: system("mkdir/rm") (std::filesystem instead).
 #include <nm03.h>
 
+#include <malloc.h>
+
 #include <algorithm>
 #include <atomic>
 #include <chrono>
@@ -122,14 +124,45 @@ class Pool {
     const int helpers = std::min<int>((int)workers_.size(), n - 1);
     {
       std::lock_guard<std::mutex> lk(mu_);
-      for (int t = 0; t < helpers; ++t) jobs_.push_back(body);
+      for (int t = 0; t < helpers; ++t) jobs_.push_front(body);   // ahead of queued export work: a feeder is waiting for this
     }
     cv_.notify_all();
     body();
     std::unique_lock<std::mutex> lk(sh->m);
     sh->cv.wait(lk, [&] { return sh->done.load() >= n; });
   }
+  // run f(0..n-1) on the pool without waiting; on_done() runs on the worker that finishes the last index.
+  // Queued behind everything else: this is the export stage, which nobody waits for until the run ends.
+  void submit_batch(int n, std::function<void(int)> f, std::function<void()> on_done) {
+    { std::lock_guard<std::mutex> lk(mu_); outstanding_ += 1; }
+    if (n <= 0 || workers_.empty()) { for (int i = 0; i < n; ++i) f(i); on_done(); return; }
+    struct Shared { std::atomic<int> next{0}, done{0}; int n; std::function<void(int)> f; std::function<void()> on_done; };
+    auto sh = std::make_shared<Shared>();
+    sh->n = n; sh->f = std::move(f); sh->on_done = std::move(on_done);
+    auto body = [sh] {
+      for (int i; (i = sh->next.fetch_add(1)) < sh->n;) {
+        sh->f(i);
+        if (sh->done.fetch_add(1) + 1 == sh->n) sh->on_done();
+      }
+    };
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      const int copies = std::min<int>((int)workers_.size(), n);
+      for (int t = 0; t < copies; ++t) jobs_.push_back(body);
+    }
+    cv_.notify_all();
+  }
+  void batch_finished() {
+    { std::lock_guard<std::mutex> lk(mu_); outstanding_ -= 1; }
+    idle_cv_.notify_all();
+  }
+  void wait_batches() {
+    std::unique_lock<std::mutex> lk(mu_);
+    idle_cv_.wait(lk, [this] { return outstanding_ == 0; });
+  }
  private:
+  int outstanding_ = 0;
+  std::condition_variable idle_cv_;
   std::vector<std::thread> workers_;
   std::deque<std::function<void()>> jobs_;
   std::mutex mu_;
@@ -180,6 +213,29 @@ void unpackMask(const uint32_t* bits, int w, int h, uint8_t* out) {
   }
 }
 
+// Pinned staging of one batch (input slices, result masks).  A feeder owns a small ring of them: a set is busy from
+// the moment its batch is read until the export jobs that render from it have finished.
+struct BufSet {
+  Pinned in, out;
+  bool busy = false;
+};
+struct BufRing {
+  std::vector<std::unique_ptr<BufSet>> sets;
+  std::mutex mu;
+  std::condition_variable cv;
+  BufSet* acquire() {
+    std::unique_lock<std::mutex> lk(mu);
+    for (;;) {
+      for (auto& s : sets) if (!s->busy) { s->busy = true; return s.get(); }
+      cv.wait(lk);
+    }
+  }
+  void release(BufSet* s) {
+    { std::lock_guard<std::mutex> lk(mu); s->busy = false; }
+    cv.notify_one();
+  }
+};
+
 void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const uint8_t* mask, int w, int h) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
@@ -200,7 +256,7 @@ void exportSlice(const fs::path& dir, const std::string& file, const int16_t* ra
 
 struct Totals {
   std::atomic<long> ok{0}, total{0}, patients_ok{0};
-  std::atomic<long> ns_list{0}, ns_parse{0}, ns_read{0}, ns_gpu{0}, ns_export{0};  // feeder wall time per phase (NM03_DRIVER_TIMING=1 prints it)
+  std::atomic<long> ns_list{0}, ns_parse{0}, ns_read{0}, ns_gpu{0}, ns_export{0}, ns_submit{0};  // feeder wall time per phase (NM03_DRIVER_TIMING=1 prints it)
   std::mutex log;
 };
 
@@ -214,7 +270,7 @@ struct PhaseTimer {   // adds the time since construction (or the last lap) to a
 };
 
 // one patient: parse on host threads into pinned memory, one GPU call per group of equal-size slices, export
-void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::string& patient, Pinned& in, Pinned& out, Totals& tot) {
+void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::string& patient, BufRing& ring, Totals& tot) {
   PhaseTimer timer;
   const fs::path outdir = fs::path(opt.out) / patient;
   if (opt.do_export || opt.dump_masks) setupOutputDirectory(outdir);
@@ -252,6 +308,10 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
           slices[j].rescale_slope == slices[first].rescale_slope && slices[j].rescale_intercept == slices[first].rescale_intercept) { idx.push_back(j); done[j] = 1; }
     const int w = slices[first].cols, h = slices[first].rows, m = (int)idx.size();
     const size_t npx = (size_t)w * h;
+    BufSet* bs = ring.acquire();          // waits while all sets of this feeder are still being exported from
+    struct Release { BufRing& r; BufSet* b; ~Release() { if (b) r.release(b); } } rel{ring, bs};
+    Pinned& in = bs->in;
+    Pinned& out = bs->out;
     in.reserve(m * npx * 2);
     std::atomic<int> read_failed{0};
     parallel_for(m, opt.host_threads, [&](int j) {
@@ -299,18 +359,47 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
         FILE* f = std::fopen((outdir / (fs::path(files[idx[j]]).stem().string() + ".mask")).string().c_str(), "wb");
         if (f) { std::fwrite(mk, 1, npx, f); std::fclose(f); }
       }
-    if (opt.do_export)
-      parallel_for(m, opt.host_threads, [&](int j) {
+    if (opt.do_export && g_pool && opt.host_threads > 1) {
+      // The export of this batch is queued on the pool and the feeder moves on to its next patient; the staging set goes
+      // back to the ring when the last slice has been written (the reference exports serially after each batch,
+      // main_parallel.cpp:346 — here that work keeps every host core busy while the GPUs go on).
+      std::vector<std::string> names;
+      for (int j = 0; j < m; ++j) names.push_back(files[idx[j]]);
+      const void* in_p = in.p;
+      const void* out_p = out.p;
+      const bool is_unsigned = params.input_unsigned != 0, byte_masks = opt.byte_masks;
+      Totals* totp = &tot;
+      BufRing* ringp = &ring;
+      Pool* pool = g_pool;
+      rel.b = nullptr;                    // ownership of the set passes to the export jobs
+      pool->submit_batch(m, [=](int j) {
+        const auto t0 = Clock::now();
         try {
           thread_local std::vector<uint8_t> scratch;
+          const uint8_t* mk;
+          if (byte_masks) mk = (const uint8_t*)out_p + j * npx;
+          else { scratch.resize(npx); unpackMask((const uint32_t*)((const uint8_t*)out_p + j * mask_bytes), w, h, scratch.data()); mk = scratch.data(); }
+          exportSlice(outdir, names[j], (const int16_t*)((const uint8_t*)in_p + j * npx * 2), is_unsigned, mk, w, h);
+        } catch (const std::exception& e) {
+          std::lock_guard<std::mutex> lk(totp->log);
+          std::cerr << "Error in export stage: " << e.what() << std::endl;
+        }
+        totp->ns_export += std::chrono::duration_cast<std::chrono::nanoseconds>(Clock::now() - t0).count();
+      }, [=] { ringp->release(bs); pool->batch_finished(); });
+      timer.lap(tot.ns_submit);
+    } else if (opt.do_export) {
+      for (int j = 0; j < m; ++j) {
+        try {
+          std::vector<uint8_t> scratch;
           exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
                       mask_of(j, scratch), w, h);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(tot.log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
         }
-      });
-    timer.lap(tot.ns_export);
+      }
+      timer.lap(tot.ns_export);
+    }
   }
   tot.ok += ok;
   tot.patients_ok += 1;
@@ -342,16 +431,19 @@ int runBatch(const Options& opt) {
   // kernels and sizes the library's device scratch.  Reported as startup_seconds.
   const int n_feeders_per_gpu = sequential ? 1 : std::max(1, opt.streams);
   const int n_gpus_used = sequential ? 1 : G;
-  std::vector<std::unique_ptr<Pinned>> ring_in, ring_out;
+  // three staging sets per feeder: one being read / on the GPU, two whose export jobs are still running
+  std::vector<std::unique_ptr<BufRing>> rings;
   for (int i = 0; i < n_gpus_used * n_feeders_per_gpu; ++i) {
-    ring_in.emplace_back(new Pinned());
-    ring_out.emplace_back(new Pinned());
-    ring_in.back()->reserve((size_t)opt.batch * 512 * 512 * 2);
-    ring_out.back()->reserve((size_t)opt.batch * 512 * 512);
+    rings.emplace_back(new BufRing());
+    for (int b = 0; b < (opt.do_export && !sequential ? 3 : 1); ++b) {
+      rings.back()->sets.emplace_back(new BufSet());
+      rings.back()->sets.back()->in.reserve((size_t)opt.batch * 512 * 512 * 2);
+      rings.back()->sets.back()->out.reserve((size_t)opt.batch * 512 * 512);
+    }
   }
   for (int g = 0; g < n_gpus_used; ++g) {
-    Pinned& in = *ring_in[g * n_feeders_per_gpu];
-    Pinned& out = *ring_out[g * n_feeders_per_gpu];
+    Pinned& in = rings[g * n_feeders_per_gpu]->sets[0]->in;
+    Pinned& out = rings[g * n_feeders_per_gpu]->sets[0]->out;
     const int m = sequential ? 1 : opt.batch;
     std::memset(in.p, 0, (size_t)m * 512 * 512 * 2);
     nm03_params params;
@@ -378,19 +470,18 @@ int runBatch(const Options& opt) {
     auto next = std::make_shared<std::atomic<int>>(lo);
     for (int s = 0; s < S; ++s)
       feeders.emplace_back([&, g, s, hi, next, inner_threads] {
-        Pinned& in = *ring_in[g * n_feeders_per_gpu + s];
-        Pinned& out = *ring_out[g * n_feeders_per_gpu + s];
+        BufRing& ring = *rings[g * n_feeders_per_gpu + s];
         for (int i; (i = next->fetch_add(1)) < hi;) {
           try {
             if (sequential) {
               Options one = opt;
               one.batch = 1;  // one slice per GPU call, as the reference's serial loop does
               one.host_threads = 1;
-              processPatient(ctx, g, one, patients[i], in, out, tot);
+              processPatient(ctx, g, one, patients[i], ring, tot);
             } else {
               Options mine = opt;
               mine.host_threads = inner_threads;
-              processPatient(ctx, g, mine, patients[i], in, out, tot);
+              processPatient(ctx, g, mine, patients[i], ring, tot);
             }
           } catch (const std::exception& e) {
             std::lock_guard<std::mutex> lk(tot.log);
@@ -400,6 +491,7 @@ int runBatch(const Options& opt) {
       });
   }
   for (auto& t : feeders) t.join();
+  pool.wait_batches();                 // the export jobs of the last batches
   g_pool = nullptr;
   const double sec = std::chrono::duration<double>(Clock::now() - t0).count();
   std::cout << "\n=== All Processing Completed ===\n\nSuccessfully processed " << tot.patients_ok << "/" << P << " patients." << std::endl;
@@ -408,8 +500,9 @@ int runBatch(const Options& opt) {
               opt.mode.c_str(), sequential ? 1 : G, P, tot.total.load(), tot.ok.load(), sec, tot.ok.load() / sec, startup,
               opt.do_export ? "true" : "false");
   if (std::getenv("NM03_DRIVER_TIMING"))
-    std::fprintf(stderr, "feeder wall time per phase, summed over feeders [ms]: list %.1f, parse %.1f, read %.1f, gpu call %.1f, export %.1f\n",
-                 tot.ns_list / 1e6, tot.ns_parse / 1e6, tot.ns_read / 1e6, tot.ns_gpu / 1e6, tot.ns_export / 1e6);
+    std::fprintf(stderr, "feeder wall time per phase, summed over feeders [ms]: list %.1f, parse %.1f, read %.1f, gpu call %.1f, export submit %.1f; "
+                 "export core time summed over pool threads %.1f\n",
+                 tot.ns_list / 1e6, tot.ns_parse / 1e6, tot.ns_read / 1e6, tot.ns_gpu / 1e6, tot.ns_submit / 1e6, tot.ns_export / 1e6);
   nm03_shutdown(ctx);
   return 0;
 }
@@ -479,6 +572,10 @@ int makeDataset(const Options& opt) {
 }  // namespace
 
 int main(int argc, char** argv) {
+  // Canvases, JPEG buffers and mask scratch are a few hundred KiB each and live for one slice: keep them on the heap
+  // (per-thread arenas) instead of one mmap/munmap pair per allocation, which serialises the export threads in the kernel.
+  mallopt(M_MMAP_THRESHOLD, 1 << 30);
+  mallopt(M_TRIM_THRESHOLD, 1 << 30);
   Options opt;
   opt.data = nm03::Config::getTestDataPath() + "Brain-Tumor-Progression/T1-Post-Combined-P001-P020/";  // main_sequential.cpp:83-84
   for (int i = 1; i < argc; ++i) {

@@ -1,7 +1,7 @@
 """The library's alternative code paths, each forced by its environment switch in a fresh process (the switches are
 read when the library is loaded): plain loads instead of TMA, no clip-floor skip list, no central-tiles-first
 order, static instead of counter-based work distribution, the exact sharpen phase instead of the fast one, a
-fixed cluster size, the warp-specialised K1, and all of them together.  Every variant must give the oracle's masks bit for bit."""
+fixed cluster size, and all of them together.  Every variant must give the oracle's masks bit for bit."""
 import os
 import subprocess
 import sys
@@ -48,7 +48,6 @@ VARIANTS = {
     "exact_sharpen": {"NM03_FORCE_EXACT_SHARPEN": "1"},
     "cluster_of_8": {"NM03_CLUSTER": "8"},
     "cluster_of_1": {"NM03_CLUSTER": "1"},
-    "warp_specialised_k1": {"NM03_K1_WS": "1"},
     "everything_off": {"NM03_NO_TMA": "1", "NM03_NO_SKIP": "1", "NM03_NO_TILE_ORDER": "1", "NM03_NO_DYNAMIC": "1",
                        "NM03_FORCE_EXACT_SHARPEN": "1"},
 }
