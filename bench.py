@@ -278,28 +278,32 @@ def link_probe(torch, dev, h2d_bytes, d2h_bytes, seconds, barrier):
             d_a.copy_(h_src, non_blocking=True)
         with torch.cuda.stream(s_out):
             h_dst.copy_(d_b, non_blocking=True)
-    barrier()
     # both copy engines stay busy the whole time: the next burst is queued before the previous one is waited for
     BURST = 16
-    reps, t0 = 0, time.perf_counter()
-    ev_prev = None
-    while time.perf_counter() - t0 < seconds:
-        for _ in range(BURST):
-            with torch.cuda.stream(s_in):
-                d_a.copy_(h_src, non_blocking=True)
-            with torch.cuda.stream(s_out):
-                h_dst.copy_(d_b, non_blocking=True)
-        ev = (s_in.record_event(), s_out.record_event())
-        if ev_prev is not None:
-            ev_prev[0].synchronize()
-            ev_prev[1].synchronize()
-            reps += BURST
-        ev_prev = ev
-    ev_prev[0].synchronize()
-    ev_prev[1].synchronize()
-    reps += BURST
-    dt = time.perf_counter() - t0
-    return reps * h2d_bytes / dt / 1e9, reps * d2h_bytes / dt / 1e9
+    best = (0.0, 0.0)
+    for _ in range(3):                       # three rounds of seconds/3, the best one counts (the first also warms the path)
+        barrier()
+        reps, t0 = 0, time.perf_counter()
+        ev_prev = None
+        while time.perf_counter() - t0 < seconds / 3:
+            for _ in range(BURST):
+                with torch.cuda.stream(s_in):
+                    d_a.copy_(h_src, non_blocking=True)
+                with torch.cuda.stream(s_out):
+                    h_dst.copy_(d_b, non_blocking=True)
+            ev = (s_in.record_event(), s_out.record_event())
+            if ev_prev is not None:
+                ev_prev[0].synchronize()
+                ev_prev[1].synchronize()
+                reps += BURST
+            ev_prev = ev
+        ev_prev[0].synchronize()
+        ev_prev[1].synchronize()
+        reps += BURST
+        dt = time.perf_counter() - t0
+        if reps * (h2d_bytes + d2h_bytes) / dt > sum(best) * 1e9:
+            best = (reps * h2d_bytes / dt / 1e9, reps * d2h_bytes / dt / 1e9)
+    return best
 
 
 def driver_io_figure(n_gpus):
@@ -585,7 +589,7 @@ def main():
     out_bufs = [{"dilated": h} for h in h_outs]
 
     run_e2e(8 * max(n_feed, depth))   # warm-up: every stream slot of the library has sized its staging buffers before the clock starts
-    h2d_gbs, d2h_gbs = link_probe(torch, dev, series_bytes, SLICES * W * H, 1.0, barrier)
+    h2d_gbs, d2h_gbs = link_probe(torch, dev, series_bytes, SLICES * W * H, 1.5, barrier)
     barrier()
     t0 = time.perf_counter()
     e2e_src0 = run_e2e(e2e_steps)
@@ -707,7 +711,8 @@ def main():
                             f"nm03_process_batch_async + nm03_wait (pinned host in/out), ONE caller thread per GPU, {depth} batches in flight"),
                     "link_h2d_gbs": link_h2d, "link_d2h_gbs": link_d2h, "link_ceiling_gbs": link_h2d + link_d2h,
                     "moved_gbs": e2e_gbs, "frac_of_link": e2e_gbs / (link_h2d + link_d2h) if link_h2d + link_d2h > 0 else None,
-                    "link_note": "raw pinned copies in the same pattern (whole-step H2D next to whole-step D2H) on all ranks at once for 1 s, summed over ranks",
+                    "link_note": "raw pinned copies in the same pattern (whole-step H2D next to whole-step D2H) on all ranks at once, best of 3 rounds, summed over ranks; "
+                                 "a ceiling for equal work per rank only roughly: on the 8-GPU box four GPUs get 16 and four 29 GB/s, and a rank that finishes early leaves its share to the others",
                     "bitpacked": None if not bits_ms else {
                         "value": world * SLICES * e2e_steps / (bits_ms * 1e-3), "unit": UNIT,
                         "d2h_bytes_per_step": SLICES * H * ((W + 31) // 32) * 4 * calls_per_step, "matches_byte_mask": bits_ok,

@@ -3,6 +3,8 @@
     ncu -i prof.ncu-rep --page raw --csv > raw.csv
     python tools/ncu_summary.py raw.csv profiles/rXy_ncu_summary.json
 
+Run it in the tree the capture was made from: the summary is stamped with the hash of the kernel sources
+(`kernel_sources_sha`), and `bench.py` ignores summaries whose stamp differs from the sources it is timing.
 One entry per kernel (the first captured launch of each name): DRAM bytes read/written, duration, registers,
 ALU/FMA pipe and issue-slot activity, executed warp instructions, active warps per cycle.
 """
@@ -55,6 +57,11 @@ def main(src, dst):
             "warp_inst": pick(row, "smsp__inst_executed.sum", "sm__inst_executed.sum"),
             "warps_active_per_cycle": pick(row, "sm__warps_active.avg.per_cycle_active"),
         }
+    # bench.py quotes a summary only when it was captured from the kernel sources it is timing
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    out["kernel_sources_sha"] = bench.kernel_sources_sha()
     json.dump(out, open(dst, "w"), indent=1)
     print(json.dumps(out, indent=1))
 
