@@ -48,6 +48,13 @@ __device__ __forceinline__ float key_to_float(int key, const PreParams& p) {
   return fminf(fmaxf(o, p.clip_min), p.clip_max);
 }
 
+// lut[idx] through the read-only path; the address is one multiply-add (base + 4 * idx)
+__device__ __forceinline__ float lut_at(const float* __restrict__ lut, uint32_t idx) {
+  unsigned long long a;
+  asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(a) : "r"(idx), "l"(lut));
+  return __ldg(reinterpret_cast<const float*>(a));
+}
+
 // NW consecutive packed words of one tile row -> registers, with the widest shared-memory loads the alignment of a
 // run allows (a run starts every RUN words: 16-byte loads when RUN % 4 == 0, 8-byte loads when RUN is even)
 template <int NW, int RUN_, int K_>
@@ -192,6 +199,29 @@ static __device__ unsigned long long g_stamps[12];
 #define NM03_STAMP(i) do { } while (0)
 #endif
 
+// The small per-CTA state of K1.  It lives at the end of the dynamic shared memory block, so the kernel has NO static
+// shared memory: the dynamic block then starts at the CTA's (1 KiB-aligned) shared window, the 128-byte alignment of the
+// TMA destination needs no run-time padding, and every tile address is a link-time constant (the padding version spent
+// ~560 k uniform-datapath instructions per launch on recomputing them).
+template <int K>
+struct K1Ctl {
+  static constexpr bool NET = K <= 9;
+  static constexpr int PR = K1_MHP + 2 * (K / 2), PWS = k1_pws(K), NRUN = K1_MW / MedianRunLen<K>::value;
+  unsigned long long bar;                                        // mbarrier of the TMA copy
+  int s_next, n_work;
+  uint32_t s_diff;
+  int pad_;
+  int s_dec[2][4];
+  uint32_t blkmax[NET ? (PR + 7) / 8 : 1][NET ? PWS / 8 : 1];
+  uint16_t worklist[NET ? K1_MHP * NRUN : 1];
+};
+
+template <int K>
+constexpr size_t k1_smem_bytes() {
+  constexpr int R = K / 2;
+  return (size_t)(K1_MHP + 2 * R) * k1_pws(K) * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * k1_pws(K) * 2 + sizeof(K1Ctl<K>);
+}
+
 template <int K, int HS, int MODE>
 __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const __grid_constant__ PreParams p,
                                                                          const __grid_constant__ CUtensorMap tmap) {
@@ -209,11 +239,13 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   static_assert(RW <= PWS, "packed tile stride too small");
   static_assert(K1_MW % RUN == 0 && RUN % 2 == 0, "median tile width must be a multiple of the (even) run length");
 
-  extern __shared__ __align__(16) uint32_t smem_raw[];
-  // TMA destination: 128-byte aligned.  The padding is added as an element offset to the __shared__ array, so the
-  // compiler keeps the shared address space (LDS/STS with 32-bit addresses); rounding the pointer through uintptr_t
-  // turned every tile access into a generic LD.E/ST.E with 64-bit address arithmetic.
-  uint32_t* smem = smem_raw + (((128u - (smem_u32(smem_raw) & 127u)) & 127u) >> 2);
+  extern __shared__ __align__(128) uint32_t smem_raw[];
+  // Layout: P | M | T | control block.  P and M are multiples of 128 bytes, so T (the TMA destination) is 128-byte
+  // aligned whenever the block is — which it is, since this kernel has no static shared memory (checked below; a
+  // misplaced block must fail loudly, not corrupt tiles).  All pointers are derived from the __shared__ array by
+  // element offsets, so the compiler keeps the shared address space (LDS/STS with 32-bit addresses).
+  uint32_t* smem = smem_raw;
+  if (smem_u32(smem_raw) & 127u) __trap();
   uint32_t* P = smem;                                         // [PR][PWS] packed keys (row q | row q+36 <<16)
   float* M = reinterpret_cast<float*>(smem + PR * PWS);    // [K1_MH][K1_MW] f(median)
 
@@ -221,8 +253,10 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   constexpr int OFF = XB - K1_HS_MAX - R;  // TMA box starts at x0-XB (16-byte rule): raw column col sits at box column col + OFF
   static_assert(OFF >= 0 && RW + OFF <= PWS, "halo does not fit the aligned TMA box");
   uint16_t* T = reinterpret_cast<uint16_t*>(M + K1_MH * K1_MW);   // [RH][PWS] raw samples of the NEXT work item (TMA destination)
-  __shared__ __align__(8) uint64_t bar;
-  __shared__ int s_next;
+  static_assert(((size_t)PR * PWS * 4) % 128 == 0 && ((size_t)K1_MH * K1_MW * 4) % 128 == 0 && ((size_t)RH * PWS * 2) % 8 == 0, "tile sizes must keep the alignment of what follows them");
+  K1Ctl<K>& ctl = *reinterpret_cast<K1Ctl<K>*>(T + RH * PWS);
+  uint64_t& bar = reinterpret_cast<uint64_t&>(ctl.bar);
+  int& s_next = ctl.s_next;
 
   const int tid = threadIdx.x;
   const int w = p.w, h = p.h;
@@ -245,7 +279,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   };
   // decode() divides by run-time values; thread 0 does it once per work item, one item ahead, and hands the result
   // to the CTA through shared memory (done by every thread it cost ~1900 cycles per item on the uniform datapath)
-  __shared__ int s_dec[2][4];
+  auto& s_dec = ctl.s_dec;
   auto issue_tma = [&](int s_, int x_, int y_) {   // one thread: bulk tensor copy of the raw halo tile of a work item
     mbar_expect_tx(&bar, RH * PWS * 2);
     tma_load_3d(T, &tmap, &bar, x_ - XB, y_ - K1_HS_MAX - R, s_);
@@ -291,25 +325,31 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       // the OFF-pixel shift is folded into the byte permutes
       const uint32_t bias2 = (bias ^ KFLIP) | ((bias ^ KFLIP) << 16);
       const uint32_t* Tw = reinterpret_cast<const uint32_t*>(T);
-#pragma unroll 3
-      for (int idx = tid; idx < PR * (PWS / 4); idx += K1_THREADS) {
-        const int q = idx / (PWS / 4), c4 = idx - q * (PWS / 4);
+      // a thread keeps its column group and walks down the rows: no division in the loop, constant pointer steps
+      constexpr int CPR = PWS / 4;                 // column groups per row
+      constexpr int RPI = K1_THREADS / CPR;        // rows in flight
+      const int qg = tid / CPR, c4 = tid - qg * CPR;
+      if (qg < RPI) {
         const int w0 = min((4 * c4 + OFF) >> 1, PWS / 2 - 2);   // first 32-bit word holding pixel 4*c4 + OFF (columns past RW are never used)
-        const uint32_t* ra = Tw + q * (PWS / 2) + w0;
-        const uint32_t* rb = Tw + (q + K1_MHP) * (PWS / 2) + w0;
-        const bool last = w0 + 2 >= PWS / 2;             // the word past the row end is never needed for real columns
-        const uint32_t a0 = ra[0], a1 = ra[1], a2 = last ? 0u : ra[2];
-        const uint32_t b0 = rb[0], b1 = rb[1], b2 = last ? 0u : rb[2];
-        uint4 o;
-        if ((OFF & 1) == 0) {
-          o.x = __byte_perm(a0, b0, 0x5410); o.y = __byte_perm(a0, b0, 0x7632);
-          o.z = __byte_perm(a1, b1, 0x5410); o.w = __byte_perm(a1, b1, 0x7632);
-        } else {
-          o.x = __byte_perm(a0, b0, 0x7632); o.y = __byte_perm(a1, b1, 0x5410);
-          o.z = __byte_perm(a1, b1, 0x7632); o.w = __byte_perm(a2, b2, 0x5410);
+        const bool last = w0 + 2 >= PWS / 2;                     // the word past the row end is never needed for real columns
+        const uint32_t* ra = Tw + qg * (PWS / 2) + w0;
+        uint32_t* dst = P + qg * PWS + 4 * c4;
+#pragma unroll 3
+        for (int q = qg; q < PR; q += RPI, ra += RPI * (PWS / 2), dst += RPI * PWS) {
+          const uint32_t* rb = ra + K1_MHP * (PWS / 2);
+          const uint32_t a0 = ra[0], a1 = ra[1], a2 = last ? 0u : ra[2];
+          const uint32_t b0 = rb[0], b1 = rb[1], b2 = last ? 0u : rb[2];
+          uint4 o;
+          if ((OFF & 1) == 0) {
+            o.x = __byte_perm(a0, b0, 0x5410); o.y = __byte_perm(a0, b0, 0x7632);
+            o.z = __byte_perm(a1, b1, 0x5410); o.w = __byte_perm(a1, b1, 0x7632);
+          } else {
+            o.x = __byte_perm(a0, b0, 0x7632); o.y = __byte_perm(a1, b1, 0x5410);
+            o.z = __byte_perm(a1, b1, 0x7632); o.w = __byte_perm(a2, b2, 0x5410);
+          }
+          if (bias2) { o.x ^= bias2; o.y ^= bias2; o.z ^= bias2; o.w ^= bias2; }   // signed input, network windows: nothing to flip
+          *reinterpret_cast<uint4*>(dst) = o;
         }
-        o.x ^= bias2; o.y ^= bias2; o.z ^= bias2; o.w ^= bias2;
-        *reinterpret_cast<uint4*>(P + q * PWS + 4 * c4) = o;
       }
     }
     if (!interior || p.border_zero) {
@@ -375,9 +415,9 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   // Work items (packed row, run of 8 columns).  An item whose whole input footprint lies at or below
   // the clip floor has a known result (skip_val) and is not sorted: 8x8-block maxima of the packed
   // tile decide that, and the remaining items are compacted into a list so that warps stay full.
-  __shared__ uint32_t blkmax[NET ? (PR + 7) / 8 : 1][NET ? PWS / 8 : 1];
-  __shared__ uint16_t worklist[NET ? K1_MHP * NRUN : 1];
-  __shared__ int n_work;
+  auto& blkmax = ctl.blkmax;
+  auto& worklist = ctl.worklist;
+  int& n_work = ctl.n_work;
   bool skip_list = NET && p.skip_on;   // items come from the compacted list (false: every item of the tile, in order)
   if constexpr (NET) if (p.skip_on) {
     if (tid == 0) n_work = 0;
@@ -475,7 +515,7 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   if (tid == 0 && p.sched) atomicAdd(reinterpret_cast<unsigned long long*>(p.sched + 2), (unsigned long long)n_items);   // nm03_profile_work
   // windows above 9x9: every key of the tile shares the bits above the highest bit in which any two of them differ
   // (12-bit data in a 16-bit word: the top four), so the rank search below starts there
-  __shared__ uint32_t s_diff;
+  uint32_t& s_diff = ctl.s_diff;
   int hb = -1;
   uint32_t prefix2 = 0u;
   if constexpr (!NET) {
@@ -552,8 +592,8 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
     if (p.lut) {
 #pragma unroll
       for (int i = 0; i < RUN; ++i) {
-        lo[i] = __ldg(p.lut + (o[i] & 0xffffu));
-        hi[i] = __ldg(p.lut + (o[i] >> 16));
+        lo[i] = lut_at(p.lut, o[i] & 0xffffu);
+        hi[i] = lut_at(p.lut, o[i] >> 16);
       }
     } else {
 #pragma unroll
@@ -696,9 +736,9 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
           if (ri >= HE && ri < HE + RB) cv[ri - HE][j] = r12[K1_HS_MAX + j];
         }
       }
+      uint32_t nibs[RB];
 #pragma unroll
       for (int r = 0; r < RB; ++r) {
-        const int oy = y0 + oyl0 + r;
         uint32_t nib = 0;
         float dmin = 3.0e38f;
 #pragma unroll
@@ -731,19 +771,32 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
             }
           }
         }
-        nib &= xmask;
-        uint32_t word = nib << (4 * (lane & 7));
-        word |= __shfl_xor_sync(0xffffffffu, word, 1);
-        word |= __shfl_xor_sync(0xffffffffu, word, 2);
-        word |= __shfl_xor_sync(0xffffffffu, word, 4);
-        if (p.predicate && (lane & 7) == 0 && oy < h) {
-          const int wi = (x0 >> 5) + (xq >> 3);
-          if (wi < p.wpr) p.predicate[((size_t)slice * h + oy) * p.wpr + wi] = word;
-        }
-        if (p.median && oy < h) {
-          const size_t rowoff = ((size_t)slice * h + oy) * w;
+        nibs[r] = nib & xmask;
+        if (p.median && y0 + oyl0 + r < h) {
+          const size_t rowoff = ((size_t)slice * h + y0 + oyl0 + r) * w;
 #pragma unroll
           for (int j = 0; j < 4; ++j) if (ox + j < w) p.median[rowoff + ox + j] = cv[r][j];
+        }
+      }
+      // Eight lanes hold the eight nibbles of one 32-pixel word, for each of the thread's four rows.  Two rows travel in
+      // the two 16-bit halves of one register through the first two exchange steps; the third step hands the low lanes the
+      // complete word of the first row of the pair and the high lanes that of the second: 3 shuffles per row pair, not 6.
+      static_assert(RB == 4, "the word assembly below pairs rows (0,1) and (2,3)");
+      const int sub = lane & 3;
+      uint32_t x01 = (nibs[0] << (4 * sub)) | (nibs[1] << (4 * sub + 16));
+      uint32_t x23 = (nibs[2] << (4 * sub)) | (nibs[3] << (4 * sub + 16));
+      x01 |= __shfl_xor_sync(0xffffffffu, x01, 1); x23 |= __shfl_xor_sync(0xffffffffu, x23, 1);
+      x01 |= __shfl_xor_sync(0xffffffffu, x01, 2); x23 |= __shfl_xor_sync(0xffffffffu, x23, 2);
+      const uint32_t y01 = __shfl_xor_sync(0xffffffffu, x01, 4), y23 = __shfl_xor_sync(0xffffffffu, x23, 4);
+      if (p.predicate && sub == 0) {
+        const bool up = (lane & 4) != 0;   // high lanes of the group: second row of each pair
+        const uint32_t wa = up ? ((y01 >> 16) | (x01 & 0xffff0000u)) : ((x01 & 0xffffu) | (y01 << 16));
+        const uint32_t wb = up ? ((y23 >> 16) | (x23 & 0xffff0000u)) : ((x23 & 0xffffu) | (y23 << 16));
+        const int wi = (x0 >> 5) + (xq >> 3), oy = y0 + oyl0 + (up ? 1 : 0);
+        if (wi < p.wpr) {
+          uint32_t* dst = p.predicate + ((size_t)slice * h + oy) * p.wpr + wi;
+          if (oy < h) dst[0] = wa;
+          if (oy + 2 < h) dst[2 * (size_t)p.wpr] = wb;
         }
       }
     }
@@ -799,7 +852,7 @@ static bool make_tmap(const PreParams& p, int R, CUtensorMap* map) {
 template <int K, int HS, int MODE>
 static cudaError_t launch_k1m(const PreParams& p0, cudaStream_t s) {
   constexpr int R = K / 2;
-  const size_t smem = (size_t)(K1_MHP + 2 * R) * k1_pws(K) * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * k1_pws(K) * 2 + 128;
+  const size_t smem = k1_smem_bytes<K>();
   PreParams p = p0;
   CUtensorMap map;
   memset(&map, 0, sizeof(map));
@@ -826,7 +879,7 @@ static cudaError_t launch_k1(const PreParams& p, int mode, cudaStream_t s) {
 template <int K, int HS>
 static cudaError_t config_k1() {
   constexpr int R = K / 2;
-  const int smem = (int)((size_t)(K1_MHP + 2 * R) * k1_pws(K) * 4 + (size_t)K1_MH * K1_MW * 4 + (size_t)(K1_MH + 2 * R) * k1_pws(K) * 2 + 128);
+  const int smem = (int)k1_smem_bytes<K>();
   cudaError_t e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k1_preprocess<K, HS, K1_FAST_FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e == cudaSuccess && HS > 2)

@@ -701,13 +701,18 @@ class RenderToImage : public ProcessObject {
 
 class ImageFileExporter : public Typed<ImageFileExporter> {
  public:
+  // FAST's exporter hands a QImage to Qt's writer without a quality argument (QImage::save(filename)); Qt's JPEG
+  // handler then uses its default, quality 75 [upstream recall, not verifiable offline].  The same default here;
+  // setQuality() is an extension for callers that want something else.
+  static constexpr int kDefaultJpegQuality = 75;
+  void setQuality(int q) { quality_ = q < 1 ? 1 : (q > 100 ? 100 : q); }
   void update() override {
     auto img = inputImage();
     if (img->getDataType() != TYPE_UINT8) throw Exception("ImageFileExporter: only 8-bit images can be written as JPEG");
     const int ch = img->getNrOfChannels();
     try {
       if (const uint8_t* plane = img->greyPlane()) {   // a grey canvas of RenderToImage: one component, no conversion
-        jpeg::save(file_, plane, img->getWidth(), img->getHeight(), 1);
+        jpeg::save(file_, plane, img->getWidth(), img->getHeight(), 1, quality_);
         return;
       }
       if (ch == 3) {  // any other RGB image: store one component when all three agree
@@ -718,11 +723,11 @@ class ImageFileExporter : public Typed<ImageFileExporter> {
         if (grey) {
           std::vector<uint8_t> g(n);
           for (size_t i = 0; i < n; ++i) g[i] = p[3 * i];
-          jpeg::save(file_, g.data(), img->getWidth(), img->getHeight(), 1);
+          jpeg::save(file_, g.data(), img->getWidth(), img->getHeight(), 1, quality_);
           return;
         }
       }
-      jpeg::save(file_, img->as<uint8_t>(), img->getWidth(), img->getHeight(), ch);
+      jpeg::save(file_, img->as<uint8_t>(), img->getWidth(), img->getHeight(), ch, quality_);
     } catch (const std::exception& e) {
       throw Exception(e.what());
     }
@@ -731,6 +736,7 @@ class ImageFileExporter : public Typed<ImageFileExporter> {
   friend class Typed<ImageFileExporter>;
   explicit ImageFileExporter(std::string file) : Typed(EXPORTER), file_(std::move(file)) {}
   std::string file_;
+  int quality_ = kDefaultJpegQuality;
 };
 
 // The 5-pane GUI of test_pipeline.cpp:148-158 needs a window system; it is left out (no graphics

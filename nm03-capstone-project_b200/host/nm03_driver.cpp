@@ -42,7 +42,7 @@ namespace {
 struct Options {
   std::string mode = "parallel", data, out = "../out-parallel", test_file, make_dataset;
   std::vector<int> gpus;
-  int batch = 25, streams = 3, host_threads = 0;   // 3 feeders per GPU measured best (21-29k slices/s from files in /dev/shm)
+  int batch = 25, streams = 0, host_threads = 0;   // feeders per GPU, 0 = choose: one when the export stage shares the pool (r2i/r2n/r2o: 1 > 2 > 3), three without export (the feeders' GPU calls then overlap each other)
   bool do_export = true, dump_masks = false, lowcontrast = false;
   bool byte_masks = false;   // --byte-masks: fetch the uint8 mask from the GPU instead of the bit-packed one (8x the bytes over the link)
   int patients = 20, slices = 24, size = 512;
@@ -600,6 +600,7 @@ int main(int argc, char** argv) {
     else { std::cerr << "unknown option " << a << std::endl; return 2; }
   }
   if (opt.host_threads <= 0) opt.host_threads = std::max(1u, std::thread::hardware_concurrency());
+  if (opt.streams <= 0) opt.streams = opt.do_export ? 1 : 3;
   if (opt.mode == "sequential" && opt.out == "../out-parallel") opt.out = "../out-sequential";
   try {
     if (!opt.make_dataset.empty()) return makeDataset(opt);
