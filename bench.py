@@ -197,7 +197,7 @@ def time_cpu(oracle, series, cfg, threads, min_seconds, max_reps):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 50 ms while the timed regions (device-resident, then e2e) run."""
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the timed regions (device-resident, then e2e) run."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -208,7 +208,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "50", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
             self.proc = None
@@ -452,9 +452,19 @@ def main():
         o.dilated = d_out[i].data_ptr()
         outs.append(o)
 
+    # everything a call needs is looked up once: the issue loop below must stay well under the 45 us a step takes on the
+    # GPU (at 8 ranks on one 32-vCPU host it is the loop, not the GPU, that a careless harness would time)
+    in_ptrs = [C.c_void_p(d_in[j].data_ptr()) for j in range(N_SERIES)]
+    stream_handles = [C.c_void_p(s.cuda_stream) for s in streams]
+    out_refs = [C.byref(o) for o in outs]
+    params_ref = C.byref(params)
+    raw_call, ctx_handle = nm03.lib().nm03_process_batch_device, ctx._h
+
     def call(j, n_str):   # one library call: one series
-        ctx.process_batch_device(d_in[j % N_SERIES].data_ptr(), SLICES, W, H, params, outs[j % len(outs)],
-                                 streams[j % n_str].cuda_stream)
+        rc = raw_call(ctx_handle, 0, in_ptrs[j % N_SERIES], SLICES, W, H, params_ref, None, 0, out_refs[j % len(outs)],
+                      stream_handles[j % n_str])
+        if rc:
+            raise nm03.Nm03Error(rc, nm03.last_error())
 
     def step(i, n_str):
         for c in range(calls_per_step):
@@ -483,13 +493,19 @@ def main():
         barrier()
         return e0.elapsed_time(e1)
 
+    # the clock sampler runs through every timed region; it is started before the warm-up and given time to deliver its
+    # first line, because nvidia-smi's start-up (NVML initialisation, device enumeration) holds driver locks that stall
+    # kernel launches of every rank for a few hundred milliseconds
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    t_wait = time.perf_counter()
+    while sampler.proc and not sampler.lines and time.perf_counter() - t_wait < 5.0:
+        time.sleep(0.05)
     for _ in range(args.warmup):
         step(next_step[0], n_streams)
         next_step[0] += 1
     barrier()
     assert int(d_out[(next_step[0] * calls_per_step - 1) % len(outs)].sum().item()) > 0, "pipeline produced empty masks"
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches0 = ctx.kernel_launches()
     regions = [timed_region(args.steps, n_streams) for _ in range(REGIONS)]
     launches = (ctx.kernel_launches() - launches0) // REGIONS   # per region of --steps steps
