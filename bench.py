@@ -571,7 +571,7 @@ def main():
         h_in[i] = d_in[i].cpu().numpy()
     n_hout = max(n_feed, depth)
     h_outs = [ctx.host_alloc((SLICES, H, W), np.uint8) for _ in range(n_hout)]
-    e2e_steps = max(4, min(args.steps, 400)) * calls_per_step
+    e2e_steps = max(60, min(args.steps, 400)) * calls_per_step   # at least 60 batches: with three in flight a shorter run is mostly ramp and drain
     e2e_params = nm03.default_params(**cfg["params"])
 
     def feeder(tid, count):
