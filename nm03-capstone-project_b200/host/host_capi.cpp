@@ -90,4 +90,35 @@ int nm03h_render_segmentation(const uint8_t* lab, int w, int h, int cw, int ch, 
   } catch (const std::exception&) { return -1; }
 }
 
+// the same two renders on the one-channel canvas the batch driver exports from (RenderToImage keeps an all-grey canvas as
+// one plane); lab_is_bits = 1: `lab` is a bit-packed {0,1} label image (nm03_outputs.dilated_bits layout)
+int nm03h_render_image_grey(const void* px, int w, int h, int is_unsigned, int cw, int ch, uint8_t* grey) {
+  try {
+    auto img = nm03::Image::view(px, w, h, is_unsigned ? nm03::TYPE_UINT16 : nm03::TYPE_INT16);
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), cw, ch);
+    rti->connect(nm03::ImageRenderer::create()->addInputData(img));
+    rti->update();
+    const uint8_t* plane = rti->getOutputData<nm03::Image>(0)->greyPlane();
+    if (!plane) return -2;
+    std::memcpy(grey, plane, (size_t)cw * ch);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
+int nm03h_render_segmentation_grey(const void* lab, int lab_is_bits, int w, int h, int cw, int ch, float opacity, float border_opacity,
+                                   int radius, uint8_t* grey) {
+  try {
+    auto img = lab_is_bits ? nm03::Image::viewBits((const uint32_t*)lab, w, h) : nm03::Image::view(lab, w, h, nm03::TYPE_UINT8);
+    nm03::LabelColors colors;
+    colors[1] = nm03::Color::White();
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), cw, ch);
+    rti->connect(nm03::SegmentationRenderer::create(colors, opacity, border_opacity, radius)->addInputData(img));
+    rti->update();
+    const uint8_t* plane = rti->getOutputData<nm03::Image>(0)->greyPlane();
+    if (!plane) return -2;
+    std::memcpy(grey, plane, (size_t)cw * ch);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
 }  // extern "C"

@@ -99,6 +99,14 @@ class Image {
     im->ext_ = pixels;
     return im;
   }
+  // a {0,1} label image held bit-packed (nm03_outputs.dilated_bits: bit x%32 of word x/32 of a row = pixel x), owned by
+  // someone else; the bytes are only unpacked if somebody asks for them (the segmentation renderer works on the words)
+  static std::shared_ptr<Image> viewBits(const uint32_t* bits, int w, int h) {
+    std::shared_ptr<Image> im(new Image(w, h, TYPE_UINT8, 1, nullptr));
+    im->bits_ = bits;
+    return im;
+  }
+  const uint32_t* labelBits() const { return bits_; }
   // an RGB canvas all of whose pixels are grey, kept as ONE channel until somebody asks for the interleaved bytes
   static std::shared_ptr<Image> greyCanvas(int w, int h, std::vector<uint8_t> plane) {
     std::shared_ptr<Image> im(new Image(w, h, TYPE_UINT8, 3, nullptr));
@@ -120,6 +128,12 @@ class Image {
   Image(int w, int h, DataType t, int channels, std::nullptr_t) : w_(w), h_(h), c_(channels), type_(t) {}
   const void* bytes() const {
     if (ext_) return ext_;
+    if (bytes_.empty() && bits_) {            // first access to the bytes of a bit-packed label image
+      bytes_.resize((size_t)w_ * h_);
+      const int wpr = (w_ + 31) / 32;
+      for (int y = 0; y < h_; ++y)
+        for (int x = 0; x < w_; ++x) bytes_[(size_t)y * w_ + x] = (bits_[(size_t)y * wpr + (x >> 5)] >> (x & 31)) & 1u;
+    }
     if (bytes_.empty() && !grey_.empty()) {   // first access to the interleaved form of a grey canvas
       bytes_.resize(grey_.size() * 3);
       for (size_t i = 0; i < grey_.size(); ++i) bytes_[3 * i] = bytes_[3 * i + 1] = bytes_[3 * i + 2] = grey_[i];
@@ -131,6 +145,7 @@ class Image {
   mutable std::vector<uint8_t> bytes_;
   std::vector<uint8_t> grey_;
   const void* ext_ = nullptr;
+  const uint32_t* bits_ = nullptr;
 };
 using Segmentation = Image;
 
@@ -524,6 +539,22 @@ class ImageRenderer : public Renderer {
       }
       size_t i = 0;
       if (stride == 1) {
+#if defined(__SSE2__)
+        // eight pixels per step with the formula of the table itself (convert, subtract, scale, clamp, round half up,
+        // truncate): the same IEEE operations per pixel, hence the same bytes as the table look-up
+        const __m128 vlo = _mm_set1_ps(lo), vinv = _mm_set1_ps(inv), v255 = _mm_set1_ps(255.0f), v0 = _mm_setzero_ps(), vh = _mm_set1_ps(0.5f);
+        const __m128i zero = _mm_setzero_si128();
+        for (; i + 8 <= n; i += 8) {
+          const __m128i s16 = _mm_loadu_si128(reinterpret_cast<const __m128i*>(ss + i));
+          const __m128i ext = sg ? _mm_srai_epi16(s16, 15) : zero;
+          __m128 g0 = _mm_mul_ps(_mm_sub_ps(_mm_cvtepi32_ps(_mm_unpacklo_epi16(s16, ext)), vlo), vinv);
+          __m128 g1 = _mm_mul_ps(_mm_sub_ps(_mm_cvtepi32_ps(_mm_unpackhi_epi16(s16, ext)), vlo), vinv);
+          g0 = _mm_add_ps(_mm_min_ps(_mm_max_ps(g0, v0), v255), vh);
+          g1 = _mm_add_ps(_mm_min_ps(_mm_max_ps(g1, v0), v255), vh);
+          const __m128i p16 = _mm_packs_epi32(_mm_cvttps_epi32(g0), _mm_cvttps_epi32(g1));
+          _mm_storel_epi64(reinterpret_cast<__m128i*>(rgb + i), _mm_packus_epi16(p16, p16));
+        }
+#endif
         for (; i < n; ++i) rgb[i] = lut[(sg ? (int)ss[i] : (int)su[i]) - lo_i];
         return;
       }
@@ -591,10 +622,11 @@ class SegmentationRenderer : public Renderer {
     auto img = inputImage();
     if (img->getDataType() != TYPE_UINT8) throw Exception("SegmentationRenderer needs a uint8 label image");
     const int w = img->getWidth(), h = img->getHeight();
-    const uint8_t* lab = img->as<uint8_t>();
-    const Fit f = fit(w, h, cw, ch);
     const Color* table[256] = {};
     for (auto& kv : colors_) if (kv.first >= 0 && kv.first < 256) table[kv.first] = &kv.second;
+    if (w == cw && h == ch && std::max(0, radius_) <= 15 && paintBits(*img, table, rgb, stride)) return;
+    const uint8_t* lab = img->as<uint8_t>();
+    const Fit f = fit(w, h, cw, ch);
     // A pixel is a border pixel when some pixel within borderRadius (disc, outside the image = label 0) carries
     // another label.  Per labelled pixel, runr = how far its label extends unbroken to both sides in its row
     // (capped at the radius); the disc test is then one comparison per row of the disc.
@@ -657,6 +689,75 @@ class SegmentationRenderer : public Renderer {
     return true;
   }
  private:
+  // The driver's case — a {0,1} label image on a canvas of its own size — on bit planes: the labelled pixels as one bit
+  // each (taken as they are from a bit-packed image, else packed here, giving up if any other label occurs), the
+  // interior = erosion of that plane by the border disc with everything outside the image counting as label 0 (row by
+  // row: AND of the row shifted by -a..a for the disc's half-width a at that row offset), and then the same blend as the
+  // general path for every set bit, with the interior or the border opacity.  Same bytes, no per-pixel neighbourhood walk.
+  bool paintBits(const Image& img, const Color* const* table, uint8_t* rgb, int stride) const {
+    const int w = img.getWidth(), h = img.getHeight(), wpr = (w + 31) / 32;
+    const Color* col = table[1];
+    std::vector<uint32_t> packed;
+    const uint32_t* L = img.labelBits();
+    if (!L) {
+      const uint8_t* lab = img.as<uint8_t>();
+      packed.assign((size_t)h * wpr, 0u);
+      for (int y = 0; y < h; ++y) {
+        const uint8_t* row = lab + (size_t)y * w;
+        uint32_t* out = packed.data() + (size_t)y * wpr;
+        int x = 0;
+#if defined(__SSE2__)
+        const __m128i one = _mm_set1_epi8(1), zero = _mm_setzero_si128();
+        for (; x + 16 <= w; x += 16) {
+          const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i*>(row + x));
+          const int is1 = _mm_movemask_epi8(_mm_cmpeq_epi8(v, one)), is0 = _mm_movemask_epi8(_mm_cmpeq_epi8(v, zero));
+          if ((is1 | is0) != 0xFFFF) return false;            // some other label: the general path handles it
+          out[x >> 5] |= (uint32_t)is1 << (x & 31);
+        }
+#endif
+        for (; x < w; ++x) {
+          if (row[x] > 1) return false;
+          out[x >> 5] |= (uint32_t)row[x] << (x & 31);
+        }
+      }
+      L = packed.data();
+    }
+    if (!col) return true;                                     // label 1 has no colour: nothing is painted
+    const int R = std::max(0, radius_);
+    int hw[31];
+    for (int b = -R; b <= R; ++b) { int a = 0; while ((a + 1) * (a + 1) + b * b <= R * R) ++a; hw[b + R] = a; }
+    auto wordAt = [&](const uint32_t* row, int k) -> uint32_t { return (k < 0 || k >= wpr) ? 0u : row[k]; };
+    // row eroded horizontally by half-width a (pixels outside the image are 0): word k of AND_{s=-a..a} (row >> s)
+    auto erodeRow = [&](const uint32_t* row, int k, int a) -> uint32_t {
+      uint32_t acc = row[k];
+      const uint32_t lo = wordAt(row, k - 1), hi = wordAt(row, k + 1);
+      for (int sft = 1; sft <= a && acc; ++sft)
+        acc &= ((row[k] >> sft) | (hi << (32 - sft))) & ((row[k] << sft) | (lo >> (32 - sft)));
+      return acc;
+    };
+    const float c[3] = {col->r, col->g, col->b};
+    for (int y = 0; y < h; ++y) {
+      const uint32_t* row = L + (size_t)y * wpr;
+      for (int k = 0; k < wpr; ++k) {
+        uint32_t m = row[k];
+        if (!m) continue;
+        uint32_t interior = m;
+        for (int b = -R; b <= R && interior; ++b) {
+          const int yy = y + b;
+          if (yy < 0 || yy >= h) { interior = 0u; break; }
+          interior &= erodeRow(L + (size_t)yy * wpr, k, hw[b + R]);
+        }
+        while (m) {
+          const int bit = __builtin_ctz(m);
+          m &= m - 1;
+          const float op = (interior >> bit & 1u) ? opacity_ : borderOpacity_;
+          uint8_t* px = rgb + ((size_t)y * w + 32 * k + bit) * stride;
+          for (int q = 0; q < stride; ++q) px[q] = (uint8_t)(int)(px[q] * (1 - op) + 255.0f * c[q] * op + 0.5f);
+        }
+      }
+    }
+    return true;
+  }
   SegmentationRenderer(LabelColors c, float o, float bo, int r) : colors_(std::move(c)), opacity_(o), borderOpacity_(bo), radius_(r) {}
   std::shared_ptr<SegmentationRenderer> me() { return std::static_pointer_cast<SegmentationRenderer>(shared_from_this()); }
   LabelColors colors_;

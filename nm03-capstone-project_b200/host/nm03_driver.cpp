@@ -236,12 +236,14 @@ struct BufRing {
   }
 };
 
-void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const uint8_t* mask, int w, int h) {
+// mask: uint8 labels, or (bits = true) the bit-packed words of nm03_outputs.dilated_bits
+void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const void* mask, bool bits, int w, int h) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
-  // views of the pinned staging buffers (they outlive this call): no copies
+  // views of the pinned staging buffers (they outlive this call): no copies, and the segmentation renderer works on the
+  // bit-packed words as they come from the GPU
   auto orig = Image::view(raw, w, h, is_unsigned ? TYPE_UINT16 : TYPE_INT16);
-  auto seg = Image::view(mask, w, h, TYPE_UINT8);
+  auto seg = bits ? Image::viewBits((const uint32_t*)mask, w, h) : Image::view(mask, w, h, TYPE_UINT8);
   LabelColors colors;
   colors[1] = Color::White();
   auto rti = RenderToImage::create(Color::Black(), 512, 512);  // main_sequential.cpp:258
@@ -375,11 +377,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       pool->submit_batch(m, [=](int j) {
         const auto t0 = Clock::now();
         try {
-          thread_local std::vector<uint8_t> scratch;
-          const uint8_t* mk;
-          if (byte_masks) mk = (const uint8_t*)out_p + j * npx;
-          else { scratch.resize(npx); unpackMask((const uint32_t*)((const uint8_t*)out_p + j * mask_bytes), w, h, scratch.data()); mk = scratch.data(); }
-          exportSlice(outdir, names[j], (const int16_t*)((const uint8_t*)in_p + j * npx * 2), is_unsigned, mk, w, h);
+          exportSlice(outdir, names[j], (const int16_t*)((const uint8_t*)in_p + j * npx * 2), is_unsigned,
+                      (const uint8_t*)out_p + j * mask_bytes, !byte_masks, w, h);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(totp->log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -390,9 +389,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     } else if (opt.do_export) {
       for (int j = 0; j < m; ++j) {
         try {
-          std::vector<uint8_t> scratch;
           exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
-                      mask_of(j, scratch), w, h);
+                      (const uint8_t*)out.p + j * mask_bytes, !opt.byte_masks, w, h);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(tot.log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;

@@ -310,3 +310,65 @@ def test_segmentation_renderer_border_rule(host, radius, canvas):
                 exp[cy, cx] = src[y, x]
     for c in range(3):
         np.testing.assert_array_equal(rgb[:, :, c], exp)
+
+
+# ---- the one-channel canvases the batch driver exports from (fast paths of both renderers) -----------------------
+@pytest.mark.parametrize("unsigned", [0, 1])
+@pytest.mark.parametrize("shape", [(64, 80), (67, 83), (512, 512)])
+def test_image_renderer_grey_canvas_matches_the_formula(host, unsigned, shape):
+    """stride-1 identity canvas: eight pixels per step with SSE2; same bytes as the scalar window/level formula."""
+    h, w = shape
+    rng = np.random.default_rng(w + unsigned)
+    img = (rng.integers(30000, 42000, shape).astype(np.uint16) if unsigned else rng.integers(-900, 3000, shape).astype(np.int16))
+    grey = np.zeros(shape, np.uint8)
+    assert host.nm03h_render_image_grey(img.ctypes.data_as(C.c_void_p), w, h, unsigned, w, h, grey.ctypes.data_as(C.c_void_p)) == 0
+    v = img.astype(np.float32)
+    lo, hi = v.min(), v.max()
+    g = (v - lo) * (np.float32(255.0) / (hi - lo))
+    exp = (np.minimum(np.float32(255), np.maximum(np.float32(0), g)) + np.float32(0.5)).astype(np.uint8)
+    np.testing.assert_array_equal(grey, exp)
+    rgb = np.zeros(shape + (3,), np.uint8)
+    assert host.nm03h_render_image(img.ctypes.data_as(C.c_void_p), w, h, unsigned, w, h, rgb.ctypes.data_as(C.c_void_p)) == 0
+    np.testing.assert_array_equal(rgb[:, :, 1], grey)
+
+
+@pytest.mark.parametrize("radius", [0, 1, 2, 3, 5])
+@pytest.mark.parametrize("shape", [(70, 90), (64, 64), (100, 131)])
+def test_segmentation_renderer_bit_planes(host, radius, shape):
+    """Identity canvas: border pixels come from an erosion on bit planes; byte labels and bit-packed labels give the same
+    canvas as scipy's erosion with the border disc (outside the image = label 0)."""
+    import scipy.ndimage as ndi
+    h, w = shape
+    rng = np.random.default_rng(radius * 7 + w)
+    lab = (ndi.gaussian_filter(rng.random(shape), 2.5) > 0.5).astype(np.uint8)
+    lab[0:6, 10:30] = 1
+    lab[h - 1, :] = 1
+    lab[:, w - 1] = 1
+    lab[40, 50] = 1
+    yy, xx = np.mgrid[-radius:radius + 1, -radius:radius + 1]
+    disc = (xx * xx + yy * yy) <= radius * radius
+    interior = ndi.binary_erosion(lab == 1, structure=disc, border_value=0) if radius > 0 else (lab == 1)
+    exp = np.zeros(shape, np.uint8)
+    exp[lab == 1] = 255
+    exp[interior] = int(np.float32(255.0) * np.float32(0.6) + np.float32(0.5))
+    wpr = (w + 31) // 32
+    padded = np.zeros((h, wpr * 32), np.uint8)
+    padded[:, :w] = lab
+    bits = np.packbits(padded, axis=1, bitorder="little").view(np.uint32).copy()
+    for src, is_bits in ((lab, 0), (bits, 1)):
+        grey = np.zeros(shape, np.uint8)
+        assert host.nm03h_render_segmentation_grey(src.ctypes.data_as(C.c_void_p), is_bits, w, h, w, h, C.c_float(0.6), C.c_float(1.0),
+                                                   radius, grey.ctypes.data_as(C.c_void_p)) == 0
+        np.testing.assert_array_equal(grey, exp, err_msg=f"bits={is_bits}")
+    # another label value sends the byte image down the general path: label 2 has no colour, label 1 next to it is border
+    lab2 = lab.copy()
+    lab2[20:24, 20:24] = 2
+    grey = np.zeros(shape, np.uint8)
+    assert host.nm03h_render_segmentation_grey(lab2.ctypes.data_as(C.c_void_p), 0, w, h, w, h, C.c_float(0.6), C.c_float(1.0), radius,
+                                               grey.ctypes.data_as(C.c_void_p)) == 0
+    assert (grey[20:24, 20:24] == 0).all()
+    interior2 = ndi.binary_erosion(lab2 == 1, structure=disc, border_value=0) if radius > 0 else (lab2 == 1)
+    exp2 = np.zeros(shape, np.uint8)
+    exp2[lab2 == 1] = 255
+    exp2[interior2] = exp[interior].max() if interior.any() else 153
+    np.testing.assert_array_equal(grey, exp2)
