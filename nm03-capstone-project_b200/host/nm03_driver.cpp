@@ -42,7 +42,7 @@ namespace {
 struct Options {
   std::string mode = "parallel", data, out = "../out-parallel", test_file, make_dataset;
   std::vector<int> gpus;
-  int batch = 25, streams = 0, host_threads = 0;   // feeders per GPU, 0 = choose: one when the export stage shares the pool (r2i/r2n/r2o: 1 > 2 > 3), three without export (the feeders' GPU calls then overlap each other)
+  int batch = 25, streams = 0, host_threads = 0;   // feeders per GPU, 0 = choose (see runBatch)
   bool do_export = true, dump_masks = false, lowcontrast = false;
   bool byte_masks = false;   // --byte-masks: fetch the uint8 mask from the GPU instead of the bit-packed one (8x the bytes over the link)
   int patients = 20, slices = 24, size = 512;
@@ -427,6 +427,11 @@ int runBatch(const Options& opt) {
   // Start-up, outside the timed region: the pinned staging ring (one in/out pair per feeder, sized for a batch of
   // 512x512 slices and grown later if a patient needs more) and one batch of blank slices per GPU, which loads the
   // kernels and sizes the library's device scratch.  Reported as startup_seconds.
+  // Feeders per GPU.  Without export the feeders' blocking GPU calls should overlap each other: three.  With export the
+  // feeders share the host with the export jobs and about three to eight of them in total are best (r2t: 1 GPU + 16 cores
+  // 10.7 k / 14.5 k / 14.7 k / 13.2 k slices/s with 1 / 2 / 3 / 4 feeders; 8 GPUs + 32 cores 22.1 k / 16.0 k / 15.5 k with
+  // 1 / 2 / 3 per GPU): three on one GPU, two each on two, one each beyond.
+  if (opt.streams <= 0) const_cast<Options&>(opt).streams = !opt.do_export ? 3 : (G >= 3 ? 1 : (G == 2 ? 2 : 3));
   const int n_feeders_per_gpu = sequential ? 1 : std::max(1, opt.streams);
   const int n_gpus_used = sequential ? 1 : G;
   // three staging sets per feeder: one being read / on the GPU, two whose export jobs are still running
@@ -598,7 +603,7 @@ int main(int argc, char** argv) {
     else { std::cerr << "unknown option " << a << std::endl; return 2; }
   }
   if (opt.host_threads <= 0) opt.host_threads = std::max(1u, std::thread::hardware_concurrency());
-  if (opt.streams <= 0) opt.streams = opt.do_export ? 1 : 3;
+
   if (opt.mode == "sequential" && opt.out == "../out-parallel") opt.out = "../out-sequential";
   try {
     if (!opt.make_dataset.empty()) return makeDataset(opt);
