@@ -128,7 +128,8 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
  * flight this way (three saturate the host link), where the reference needs its 16 OpenMP threads
  * (main_parallel.cpp:336-343,401) to overlap anything.  At most 8 tickets per GPU can be outstanding: with all
  * slots taken the call returns NM03_ERR_BUSY instead of blocking (the caller may hold every ticket itself).
- * nm03_wait may be called from any thread, once per ticket. */
+ * nm03_wait may be called from any thread, once per ticket; every ticket must be waited for before nm03_shutdown (a ticket
+ * holds one of the context's stream slots, and an unwaited one is leaked). */
 typedef struct nm03_ticket nm03_ticket;
 int nm03_process_batch_async(nm03_ctx* ctx, int gpu, const void* slices, int n, int w, int h, const nm03_params* params,
                              const int* seeds_xy, int n_seeds, const nm03_outputs* out, nm03_ticket** ticket);

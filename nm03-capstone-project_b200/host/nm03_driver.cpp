@@ -405,7 +405,7 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
   std::cout << "Patient " << patient << " completed. Successfully processed " << ok << "/" << n << " images." << std::endl;
 }
 
-int runBatch(const Options& opt) {
+int runBatch(Options opt) {
   const auto t_start = Clock::now();
   const std::vector<std::string> patients = findAllPatientDirectories(opt.data);
   std::cout << "Found " << patients.size() << " patient directories." << std::endl;
@@ -431,7 +431,7 @@ int runBatch(const Options& opt) {
   // feeders share the host with the export jobs and about three to eight of them in total are best (r2t: 1 GPU + 16 cores
   // 10.7 k / 14.5 k / 14.7 k / 13.2 k slices/s with 1 / 2 / 3 / 4 feeders; 8 GPUs + 32 cores 22.1 k / 16.0 k / 15.5 k with
   // 1 / 2 / 3 per GPU): three on one GPU, two each on two, one each beyond.
-  if (opt.streams <= 0) const_cast<Options&>(opt).streams = !opt.do_export ? 3 : (G >= 3 ? 1 : (G == 2 ? 2 : 3));
+  if (opt.streams <= 0) opt.streams = !opt.do_export ? 3 : (G >= 3 ? 1 : (G == 2 ? 2 : 3));
   const int n_feeders_per_gpu = sequential ? 1 : std::max(1, opt.streams);
   const int n_gpus_used = sequential ? 1 : G;
   // three staging sets per feeder: one being read / on the GPU, two whose export jobs are still running
