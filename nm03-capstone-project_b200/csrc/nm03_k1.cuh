@@ -419,9 +419,12 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
   auto& worklist = ctl.worklist;
   int& n_work = ctl.n_work;
   bool skip_list = NET && p.skip_on;   // items come from the compacted list (false: every item of the tile, in order)
+  int n_uniform = skip_list ? -1 : K1_MHP * NRUN;   // >= 0: the number of items is known without the list (all of them, or none)
   if constexpr (NET) if (p.skip_on) {
     if (tid == 0) n_work = 0;
     constexpr int NBLK = ((PR + 7) / 8) * (PWS / 8);
+    static_assert(2 * NBLK <= K1_THREADS, "two threads per block of maxima, all blocks in one trip (the vote below counts threads)");
+    bool above = false;
     for (int base = 0; base < 2 * NBLK; base += K1_THREADS) {   // two threads per 8x8 block, four rows each (block-uniform trips)
       const int bidx = (base + tid) >> 1, half = tid & 1;
       const int g = bidx / (PWS / 8), c8 = bidx - g * (PWS / 8);
@@ -439,23 +442,22 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
         }
       }
       m = __vmaxs2(m, __shfl_xor_sync(0xffffffffu, m, 1));
-      if (bidx < NBLK && half == 0) blkmax[g][c8] = m;
+      if (bidx < NBLK && half == 0) { blkmax[g][c8] = m; above = __vmaxs2(m, p.skip_key2) != p.skip_key2; }
     }
-    __syncthreads();
     NM03_STAMP(10);
-    // Whole-tile shortcuts (two block-wide votes over the block maxima): a tile in which EVERY 8x8 block holds a sample
-    // above the floor needs every window sorted (no list: brain interior), a tile in which NO block does needs none
-    // (air: the median tile is the floor value); only mixed tiles build the list.
-    static_assert(NBLK <= K1_THREADS, "one thread per block of maxima");
-    bool above = false;
-    if (tid < NBLK) { const uint32_t bm = blkmax[tid / (PWS / 8)][tid % (PWS / 8)]; above = __vmaxs2(bm, p.skip_key2) != p.skip_key2; }
-    const int any_above = __syncthreads_or(above), all_above = __syncthreads_and(tid >= NBLK || above);
-    if (!any_above) {
+    // Whole-tile shortcuts: a tile in which EVERY 8x8 block holds a sample above the floor needs every window sorted (no
+    // list: brain interior), a tile in which NO block does needs none (air: the median tile is the floor value); only
+    // mixed tiles build the list.  One counting barrier publishes the block maxima and takes the vote (the thread that
+    // wrote a block's maximum votes for it).
+    const int n_above = __syncthreads_count(above);
+    if (n_above == 0) {
+      skip_list = false;
+      n_uniform = 0;
       const float4 f4 = make_float4(p.skip_val, p.skip_val, p.skip_val, p.skip_val);
       for (int i = tid; i < K1_MH * K1_MW / 4; i += K1_THREADS) reinterpret_cast<float4*>(M)[i] = f4;
-    } else if (all_above) {
+    } else if (n_above == NBLK) {
       skip_list = false;
-      if (tid == 0) n_work = K1_MHP * NRUN;
+      n_uniform = K1_MHP * NRUN;
     } else {
     const int lane = tid & 31;
     // every thread rates its (up to ROUNDS) items first, then each warp reserves room in the list once
@@ -507,11 +509,11 @@ __global__ void __launch_bounds__(K1_THREADS, K1_MIN_CTAS) k1_preprocess(const _
       if (need[r]) worklist[slot + __popc(bal[r] & ((1u << lane) - 1u))] = (uint16_t)(r * K1_THREADS + tid);
       slot += __popc(bal[r]);
     }
+    __syncthreads();   // the list and its length are complete (tiles that took a shortcut above need no barrier here)
     }
-    __syncthreads();
   }
   NM03_STAMP(3);
-  const int n_items = (NET && p.skip_on) ? n_work : K1_MHP * NRUN;
+  const int n_items = n_uniform >= 0 ? n_uniform : n_work;
   if (tid == 0 && p.sched) atomicAdd(reinterpret_cast<unsigned long long*>(p.sched + 2), (unsigned long long)n_items);   // nm03_profile_work
   // windows above 9x9: every key of the tile shares the bits above the highest bit in which any two of them differ
   // (12-bit data in a 16-bit word: the top four), so the rank search below starts there
