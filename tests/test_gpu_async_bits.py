@@ -133,3 +133,43 @@ def test_work_counter_counts_sorted_median_items(lib):
     all_items = 4 * 32 * 36 * 17            # slices x tiles x packed rows x runs of 8 columns
     assert 0.3 * all_items < n < all_items, (n, all_items)   # the air around the head takes the clip-floor shortcut
     assert 1000 < lib.median_network_ops(7) < 1500 and lib.median_network_ops(4) == 0
+
+
+def test_prepared_parameter_blocks_are_keyed_by_everything_they_depend_on(lib):
+    """The library caches the prepared kernel parameter blocks per (parameters, size, seeds, requested planes).  One context,
+    parameter sets and sizes interleaved over several rounds — every call must give what a fresh context gives: the oracle's."""
+    rng = np.random.default_rng(3)
+    cases = [
+        (_series(2, 256, 256, 21), dict(), None, ("dilated",)),
+        (_series(2, 256, 256, 21), dict(median_window=5, dilate_size=7), None, ("dilated",)),
+        (_series(2, 200, 150, 22), dict(), None, ("dilated", "sharpened")),
+        (_series(2, 256, 256, 21), dict(), np.array([[128, 128], [100, 90], [5, 5]], np.int32), ("dilated",)),
+        (_series(2, 256, 256, 21), dict(), np.array([[5, 5], [10, 10], [6, 5]], np.int32), ("dilated",)),   # same count, other points: empty mask
+        (_series(2, 256, 256, 23, "lowcontrast"), dict(erode_size=3), None, ("dilated", "eroded")),
+        (_series(2, 256, 256, 21).astype(np.uint16), dict(), None, ("dilated",)),
+    ]
+    expected = []
+    for raw, kw, seeds, want in cases:
+        p = cm.oparams(**kw)
+        if raw.dtype == np.uint16:
+            p.input_unsigned = 1
+        exp = []
+        for i in range(len(raw)):
+            if seeds is None:
+                rc, one = cm.o_pipeline(raw[i], p)
+            else:
+                f = cm.o_clip(cm.o_normalize(raw[i]))
+                sh = cm.o_sharpen(cm.o_median(f, 7))
+                rc, rg, _ = cm.o_region_grow(sh, 0.74, 0.91, seeds)
+                one = {"dilated": cm.o_dilate(rg, 3)[1], "sharpened": sh}
+            assert rc == 0
+            exp.append(one)
+        expected.append(exp)
+    with lib.Context([0]) as ctx:
+        for rnd in range(4):
+            for idx in rng.permutation(len(cases)):
+                raw, kw, seeds, want = cases[idx]
+                got = ctx.process_batch(raw, lib.default_params(**kw), seeds=seeds, want=want)
+                for i in range(len(raw)):
+                    for name in want:
+                        np.testing.assert_array_equal(got[name][i], expected[idx][i][name], err_msg=f"round {rnd} case {idx} {name}")
