@@ -27,3 +27,12 @@ def test_reference_arm_other_ranks_exit_quietly():
     r = subprocess.run([sys.executable, os.path.join(cm.ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
                         "--warmup", "0"], env=env, capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_reference_arm_follows_the_config():
+    r = subprocess.run([sys.executable, os.path.join(cm.ROOT, "bench.py"), "--impl", "reference", "--config", "c5", "--steps", "1",
+                        "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][0])
+    assert d["impl"] == "reference" and "low-contrast" in d["config"]["workload"] and d["scaling"] == "weak"
+    assert d["value"] > 0 and "24-slice 512x512" in d["cpu_baseline"]["sample"]
