@@ -127,7 +127,9 @@ int nm03_process_batch(nm03_ctx* ctx, int gpu, const void* slices, int n, int w,
  * memory the copies fall back to staged, partly synchronous transfers.  One host thread can keep several batches in
  * flight this way (three saturate the host link), where the reference needs its 16 OpenMP threads
  * (main_parallel.cpp:336-343,401) to overlap anything.  At most 8 tickets per GPU can be outstanding: with all
- * slots taken the call returns NM03_ERR_BUSY instead of blocking (the caller may hold every ticket itself).
+ * slots taken the call returns NM03_ERR_BUSY instead of blocking (the caller may hold every ticket itself).  The blocking
+ * entry points, by contrast, wait for a free slot: a thread that holds all eight tickets of a GPU must wait for one before
+ * it calls them on that GPU.
  * nm03_wait may be called from any thread, once per ticket; every ticket must be waited for before nm03_shutdown (a ticket
  * holds one of the context's stream slots, and an unwaited one is leaked). */
 typedef struct nm03_ticket nm03_ticket;
