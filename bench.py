@@ -318,6 +318,10 @@ def driver_io_figure(n_gpus):
     gpus = ",".join(str(i) for i in range(n_gpus))
     try:
         shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None   # memory-backed: no disk in the figure
+        if shm:
+            st = os.statvfs(shm)
+            if st.f_bavail * st.f_frsize < (2 << 30):
+                shm = None                       # a small tmpfs (container default 64 MiB): the ordinary temp dir instead
         free = os.statvfs(shm or tempfile.gettempdir())
         big = 120 if free.f_bavail * free.f_frsize > (6 << 30) else 40
         out = {"gpus": n_gpus, "host_cores": host_threads()}
@@ -351,7 +355,7 @@ def driver_io_figure(n_gpus):
                     done = r.stdout.count("Successfully processed 24/24 images")
                     out["reference_driver_on_shim"] = {"slices_per_sec": done * 24 / dt, "patients_ok": done, "seconds": dt,
                                                        "note": "reference main_parallel.cpp compiled unchanged against host/compat + libnm03.so, 1 GPU, wall time of the whole process incl. start-up and JPEG export"}
-        out["sample"] = "DICOM files in a memory-backed temp dir, timed after context start-up, best of two runs each"
+        out["sample"] = ("DICOM files in " + ("a memory-backed temp dir" if shm else "the temp dir") + ", timed after context start-up, best of two runs each")
         return out
     except Exception as e:  # informational only
         return {"error": f"{type(e).__name__}: {str(e)[:200]}"}
