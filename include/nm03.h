@@ -53,7 +53,7 @@ enum { NM03_MORPH_DILATE = 0, NM03_MORPH_ERODE = 1 };
 typedef struct nm03_params {
   float norm_low, norm_high, norm_min, norm_max; /* IntensityNormalization::create(0.5f,2.5f,0.0f,10000.0f) main_sequential.cpp:195-196 */
   float clip_min, clip_max;                      /* IntensityClipping::create(0.68f,4000.0f)     main_sequential.cpp:200 */
-  int median_window;                             /* VectorMedianFilter::create(7)                main_sequential.cpp:204; any odd size 3..15 */
+  int median_window;                             /* VectorMedianFilter::create(7)                main_sequential.cpp:204; any odd size 3..255 (above 15: two passes, clamp-to-edge border only) */
   float sharpen_gain, sharpen_sigma;             /* ImageSharpening::create(2.0f,0.5f,9)         main_sequential.cpp:208 */
   int sharpen_mask;
   float rg_min, rg_max;                          /* SeededRegionGrowing::create(0.74f,0.91f,..)  main_sequential.cpp:232-233 */

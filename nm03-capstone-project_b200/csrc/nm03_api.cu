@@ -83,6 +83,8 @@ struct Slot {
   size_t sched_bytes = 0;
   float* lut = nullptr;           // scratch: f(key) table of K1 for the parameters in lut_key
   size_t lut_bytes = 0;
+  void* bigmed = nullptr;         // scratch: raw-sample median plane [n][h][w] of windows above 15x15 (two-pass path)
+  size_t bigmed_bytes = 0;
   float lut_key[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool lut_valid = false;
   bool busy = false;
@@ -230,8 +232,11 @@ int check_params(const nm03_params* p, int w, int h, bool whole_pipeline) {
 int check_preprocess(const nm03_params* p, int* sharpen_half) {
   if (p->median_window < 3 || (p->median_window & 1) == 0)
     return fail(NM03_ERR_PARAM, "median window must be odd and >= 3, got %d", p->median_window);
-  if (p->median_window > 15)
-    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (odd sizes 3..15 are)", p->median_window);
+  if (p->median_window > nm03::BIG_MAX_WINDOW)
+    return fail(NM03_ERR_UNSUPPORTED, "median window %d not implemented (odd sizes 3..%d are)", p->median_window, nm03::BIG_MAX_WINDOW);
+  if (p->median_window > nm03::K1_MAX_WINDOW && p->border_mode == NM03_BORDER_ZERO)
+    return fail(NM03_ERR_UNSUPPORTED, "zero border mode is implemented for median windows up to %d, got %d", nm03::K1_MAX_WINDOW,
+                p->median_window);
   int m = p->sharpen_mask;
   if (m == 0) m = (int)std::ceil(2.0f * p->sharpen_sigma) * 2 + 1;  // FAST's default mask size
   if (m < 1 || (m & 1) == 0) return fail(NM03_ERR_PARAM, "sharpen mask size must be odd, got %d", m);
@@ -283,7 +288,8 @@ int fill_pre(nm03::PreParams& k, const nm03_params* p, int n, int w, int h, int 
   // clip floor shortcut: the largest key K with f(K) == f(lowest key); f must be non-decreasing in the
   // key (both normalisation factors of one sign) and the zero-border sentinel must not be in play
   k.skip_on = 0; k.skip_key2 = 0; k.skip_val = 0.0f;
-  if (!g_no_skip && !k.border_zero && p->median_window <= 9 && (double)k.norm_scale * (double)k.norm_range > 0.0) {
+  if (!g_no_skip && !k.border_zero && (p->median_window <= 9 || p->median_window > nm03::K1_MAX_WINDOW) &&
+      (double)k.norm_scale * (double)k.norm_range > 0.0) {   // network windows, and the 1x1 pass of windows above 15
     const int kmin = -32768, off = k.input_unsigned ? 32768 : 0;
     const float fmin_ = f_host((float)(kmin + off), p);
     int lo = kmin, hi = 32767;                        // invariant: f(lo) == fmin_
@@ -550,6 +556,25 @@ int run_segment(Worker* wk, Slot* s, cudaStream_t st, const nm03::SegParams& seg
 }
 
 // make sure the slot's f(key) table matches these parameters (rebuilt by a tiny kernel when they change)
+// K1 for any supported window.  Up to 15x15 the fused kernel does everything; above, the window median of the raw
+// samples is taken first (generic kernel, slot scratch) and K1 runs on that plane with the 1x1 window.  The caller has
+// ordered the stream after the slot's previous use.
+int launch_preprocess_any(Slot* s, nm03::PreParams& pre, int median_window, int hs, int k1_mode, cudaStream_t st) {
+  if (median_window <= nm03::K1_MAX_WINDOW) {
+    CK(nm03::launch_preprocess(pre, median_window, hs, k1_mode, st));
+    return NM03_OK;
+  }
+  int rc;
+  if ((rc = ensure(s, &s->bigmed, &s->bigmed_bytes, (size_t)pre.n * pre.w * pre.h * 2))) return rc;
+  CK(nm03::launch_median_big(pre.in, pre.n, pre.w, pre.h, median_window, pre.input_unsigned, s->bigmed, st));
+  const void* in0 = pre.in;
+  pre.in = s->bigmed;
+  const cudaError_t e = nm03::launch_preprocess(pre, 1, hs, k1_mode, st);
+  pre.in = in0;
+  CK(e);
+  return NM03_OK;
+}
+
 int ensure_lut(Worker* wk, Slot* s, cudaStream_t st, nm03::PreParams& pre) {
   int rc;
   if ((rc = ensure(s, (void**)&s->lut, &s->lut_bytes, 65536 * sizeof(float)))) return rc;
@@ -634,7 +659,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
     else for (auto& e : rec.e) CK(cudaEventCreate(&e));
   }
   if (prof) CK(cudaEventRecord(rec.e[0], st));
-  CK(nm03::launch_preprocess(pre, p->median_window, hs, k1_mode, st));
+  if ((rc = launch_preprocess_any(s, pre, p->median_window, hs, k1_mode, st))) return rc;
   if (prof) CK(cudaEventRecord(rec.e[1], st));
   seg.pred = s->pred;
   seg.dilated = d_out->dilated;
@@ -701,6 +726,9 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
   if (n == 0) return NM03_OK;
   if ((rc = check_params(params, w, h, true))) return rc;
   if ((rc = check_preprocess(params, &hs))) return rc;
+  if (params->median_window > nm03::K1_MAX_WINDOW)
+    return fail(NM03_ERR_UNSUPPORTED, "median windows above %d need scratch memory for a second pass and are only available through "
+                "nm03_process_batch_device, got %d", nm03::K1_MAX_WINDOW, params->median_window);
   const long long wpr = (w + 31) / 32;
   const long long words = (long long)n * h * wpr;
   if (words > (long long)NM03_NOALLOC_MAX_PRED_WORDS) {
@@ -837,6 +865,7 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.stage_in) cudaFree(s.stage_in);
       if (s.stage_out) cudaFree(s.stage_out);
       if (s.lut) cudaFree(s.lut);
+      if (s.bigmed) cudaFree(s.bigmed);
       if (s.sched) cudaFree(s.sched);
       if (s.gmask) cudaFree(s.gmask);
       if (s.dflag) cudaFree(s.dflag);
@@ -1182,7 +1211,7 @@ int nm03_preprocess(nm03_ctx* ctx, int gpu, const void* slice, int w, int h, con
   pre.sharpened = sharpened ? (float*)(so + npx * 4) : nullptr;
   pre.predicate = predicate ? (uint32_t*)(so + npx * 8) : nullptr;
   const int k1_mode = (sharpened || g_force_exact) ? nm03::K1_EXACT : fill_fast(pre, params, hs);
-  CK(nm03::launch_preprocess(pre, params->median_window, hs, k1_mode, s->stream));
+  if ((rc = launch_preprocess_any(s, pre, params->median_window, hs, k1_mode, s->stream))) return rc;
   wk->launches += 1;
   if (median) CK(cudaMemcpyAsync(median, pre.median, npx * 4, cudaMemcpyDeviceToHost, s->stream));
   if (sharpened) CK(cudaMemcpyAsync(sharpened, pre.sharpened, npx * 4, cudaMemcpyDeviceToHost, s->stream));

@@ -106,6 +106,11 @@ size_t seg_smem_bytes(int rows_per, int wpr);
 
 // launchers (return cudaError_t of the launch)
 cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen_half, int mode, cudaStream_t s);
+// windows above K1_MAX_WINDOW: window median of the raw 16-bit samples (clamp-to-edge) into `out` [n][h][w], same sample
+// type as the input; K1 then runs on that plane with the 1x1 window (median_window = 1 above)
+constexpr int K1_MAX_WINDOW = 15;      // largest window K1 evaluates itself (tile halo)
+constexpr int BIG_MAX_WINDOW = 255;    // largest window of the two-pass path
+cudaError_t launch_median_big(const void* in, int n, int w, int h, int window, int input_unsigned, void* out, cudaStream_t s);
 cudaError_t launch_segment(const SegParams& p, cudaStream_t s);
 // global-memory fallback (SegParams::cluster == 0): band-wise fill pass over the bit-packed mask, then morphology
 cudaError_t launch_band_fill(const SegParams& p, uint32_t* gmask, int* gflag, int first_launch, cudaStream_t s);

@@ -95,6 +95,17 @@ NM03_DEFINE_MEDIAN_RUN(5)
 NM03_DEFINE_MEDIAN_RUN(7)
 NM03_DEFINE_MEDIAN_RUN(9)
 #undef NM03_DEFINE_MEDIAN_RUN
+// 1x1 "window": the median of one sample is the sample.  Second pass of the two-pass path for windows above 15x15
+// (launch_median_big computes the window median of the raw samples first; median and f() commute).
+template <>
+struct MedianRun<1> {
+  static constexpr int RUN = 8;
+  static __device__ __forceinline__ void run(uint32_t (&v)[RUN][1], uint32_t (&o)[RUN]) {
+#pragma unroll
+    for (int i = 0; i < RUN; ++i) o[i] = v[i][0];
+  }
+};
+template <> struct MedianRunLen<1> { static constexpr int value = MedianRun<1>::RUN; };
 template <> struct MedianRunLen<3> { static constexpr int value = MedianRun<3>::RUN; };
 template <> struct MedianRunLen<5> { static constexpr int value = MedianRun<5>::RUN; };
 template <> struct MedianRunLen<7> { static constexpr int value = MedianRun<7>::RUN; };

@@ -3,7 +3,7 @@
 #include "nm03_k1.cuh"
 
 #ifndef NM03_K1_WINDOW
-#error "compile with -DNM03_K1_WINDOW=<3|5|7|9|11|13|15>"
+#error "compile with -DNM03_K1_WINDOW=<1|3|5|7|9|11|13|15>"
 #endif
 #define NM03_CAT_(a, b) a##b
 #define NM03_CAT(a, b) NM03_CAT_(a, b)

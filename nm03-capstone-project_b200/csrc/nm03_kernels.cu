@@ -28,7 +28,7 @@ cudaError_t launch_build_lut(const PreParams& p, float* lut, cudaStream_t s) {
 }
 
 // K1 is instantiated per median window in its own translation unit (nm03_k1_w.cu with -DNM03_K1_WINDOW=k)
-#define NM03_K1_WINDOWS(X) X(3) X(5) X(7) X(9) X(11) X(13) X(15)
+#define NM03_K1_WINDOWS(X) X(1) X(3) X(5) X(7) X(9) X(11) X(13) X(15)
 #define NM03_DECL(k) cudaError_t launch_k1_w##k(const PreParams& p, int sharpen_half, int mode, cudaStream_t s); cudaError_t config_k1_w##k();
 NM03_K1_WINDOWS(NM03_DECL)
 #undef NM03_DECL
@@ -50,6 +50,66 @@ cudaError_t launch_preprocess(const PreParams& p, int median_window, int sharpen
 #undef NM03_CASE
     default: return cudaErrorInvalidValue;
   }
+}
+
+// =================================================================================================
+// Windows above 15x15: generic median of the raw samples, one output per thread
+// =================================================================================================
+// The tile halo of K1 ends at 15x15.  FAST's VectorMedianFilter takes any odd window (main_sequential.cpp:204), so larger
+// ones go through two passes: this kernel writes the K x K median of the RAW 16-bit samples (coordinates clamped to the
+// edge, nm03o_median) and K1 runs on that plane with a 1x1 window — normalise + clip is monotone, so it commutes with
+// the median (the same identity K1 itself rests on).  Exact for every input, ties included, and deliberately simple:
+// a bound on the window's values, then a most-significant-bit-first search for the sample of rank (K*K+1)/2, counting
+// the samples below a trial value.  About 3 * (2 + bits that differ) * K*K instructions per pixel, read through L1.
+__global__ void __launch_bounds__(256) k_median_big(const uint16_t* __restrict__ in, uint16_t* __restrict__ out, int w, int h, int R,
+                                                    uint32_t flip) {
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= w || y >= h) return;
+  const uint16_t* __restrict__ img = in + (size_t)blockIdx.z * w * h;
+  const int K = 2 * R + 1;
+  const uint32_t rank = (uint32_t)(K * K + 1) / 2;
+  // unsigned order: signed samples are flipped by 0x8000
+  uint32_t mn = 0xffffu, mx = 0u;
+  for (int dy = -R; dy <= R; ++dy) {
+    const uint16_t* __restrict__ row = img + (size_t)min(max(y + dy, 0), h - 1) * w;
+    for (int dx = -R; dx <= R; ++dx) {
+      const uint32_t v = (uint32_t)__ldg(row + min(max(x + dx, 0), w - 1)) ^ flip;
+      mn = min(mn, v);
+      mx = max(mx, v);
+    }
+  }
+  uint32_t cand = mn;
+  if (mn != mx) {
+    const int hb = 31 - __clz((int)(mn ^ mx));   // every sample shares the bits above hb
+    cand = mn & ~((2u << hb) - 1u);
+    for (int b = hb; b >= 0; --b) {
+      const uint32_t t = cand | (1u << b);
+      uint32_t below = 0u;
+      for (int dy = -R; dy <= R; ++dy) {
+        const uint16_t* __restrict__ row = img + (size_t)min(max(y + dy, 0), h - 1) * w;
+        for (int dx = -R; dx <= R; ++dx)
+          below += (((uint32_t)__ldg(row + min(max(x + dx, 0), w - 1)) ^ flip) < t) ? 1u : 0u;
+      }
+      if (below < rank) cand = t;   // fewer than `rank` samples below t: the median is at least t
+    }
+  }
+  out[(size_t)blockIdx.z * w * h + (size_t)y * w + x] = (uint16_t)(cand ^ flip);
+}
+
+cudaError_t launch_median_big(const void* in, int n, int w, int h, int window, int input_unsigned, void* out, cudaStream_t s) {
+  if (window < 3 || (window & 1) == 0 || window > BIG_MAX_WINDOW || n <= 0) return cudaErrorInvalidValue;
+  const int gy = (h + 7) / 8;
+  if (gy > 65535) return cudaErrorInvalidValue;
+  for (int z0 = 0; z0 < n; z0 += 65535) {   // gridDim.z limit
+    const int nz = n - z0 < 65535 ? n - z0 : 65535;
+    const dim3 grid((unsigned)((w + 31) / 32), (unsigned)gy, (unsigned)nz);
+    const size_t off = (size_t)z0 * w * h;
+    k_median_big<<<grid, 256, 0, s>>>(reinterpret_cast<const uint16_t*>(in) + off, reinterpret_cast<uint16_t*>(out) + off, w, h,
+                                      window / 2, input_unsigned ? 0u : 0x8000u);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 // =================================================================================================

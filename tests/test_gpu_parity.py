@@ -250,11 +250,11 @@ def test_pipeline_ragged_and_switches(lib, ctx):
 
 
 def test_pipeline_median_window_9_and_unsupported_windows(lib, ctx):
-    """N4 generality: 9x9 is implemented (slower network); windows above 15 are refused, even ones are
+    """N4 generality: 9x9 is implemented (slower network); windows above 255 are refused, even ones are
     a parameter error as in FAST."""
     raws = np.stack([cm.phantom(300, 260, 9, i) for i in range(2)])
     _cmp_pipeline(lib, ctx, raws, median_window=9, dilate_size=5)
-    for k, code in ((17, lib.ERR_UNSUPPORTED), (4, lib.ERR_PARAM), (1, lib.ERR_PARAM)):
+    for k, code in ((257, lib.ERR_UNSUPPORTED), (4, lib.ERR_PARAM), (1, lib.ERR_PARAM)):
         with pytest.raises(lib.Nm03Error) as e:
             ctx.process_batch(raws, lib.default_params(median_window=k))
         assert e.value.code == code
@@ -282,6 +282,32 @@ def test_preprocess_large_windows_value_ranges_and_borders(lib, ctx, k):
 def test_pipeline_median_window_13(lib, ctx):
     raws = np.stack([cm.phantom(512, 512, 9, i) for i in range(3)])
     _cmp_pipeline(lib, ctx, raws, median_window=13, dilate_size=5, erode_size=3)
+
+
+# ---- median windows above 15: two passes (generic median of the raw samples, then K1 with a 1x1 window) ----------
+@pytest.mark.parametrize("k", [17, 21, 33])
+def test_preprocess_windows_above_15(lib, ctx, k):
+    _cmp_pre(lib, ctx, cm.phantom(160, 110, 2, k), median_window=k, sharpen_mask=3 if k == 21 else 9, sharpen_sigma=0.8)
+    _cmp_fast(lib, ctx, cm.phantom(200, 136, 2, k + 1), median_window=k)        # fast predicate mode on the median plane
+
+
+def test_preprocess_windows_above_15_value_ranges_and_borders(lib, ctx):
+    rng = np.random.default_rng(17)
+    _cmp_pre(lib, ctx, rng.integers(-32768, 32768, (90, 77)).astype(np.int16), median_window=17)    # all 16 bits in play
+    _cmp_pre(lib, ctx, rng.integers(0, 65536, (64, 96)).astype(np.uint16), median_window=19)
+    _cmp_pre(lib, ctx, rng.integers(1195, 1206, (70, 66)).astype(np.int16), median_window=23)       # heavy ties
+    _cmp_pre(lib, ctx, np.full((40, 50), 1200, np.int16), median_window=17)                          # one value only
+    _cmp_pre(lib, ctx, cm.phantom(60, 44, 4, 2), median_window=101)                                  # window larger than the image
+    _cmp_pre(lib, ctx, cm.phantom(517, 203, 4, 2), median_window=17)                                 # no TMA (width % 8), ragged tiles
+    with pytest.raises(lib.Nm03Error) as e:                                                          # zero border: up to 15 only
+        ctx.preprocess(cm.phantom(120, 120, 1, 1), lib.default_params(median_window=17, border_mode=1))
+    assert e.value.code == lib.ERR_UNSUPPORTED
+
+
+def test_pipeline_median_window_25(lib, ctx):
+    raws = np.stack([cm.phantom(256, 200, 9, i) for i in range(3)])
+    _cmp_pipeline(lib, ctx, raws, median_window=25, dilate_size=5, erode_size=3)
+    _cmp_pipeline(lib, ctx, raws.astype(np.uint16), median_window=17, input_unsigned=1)
 
 
 def test_pipeline_dimension_guard(lib, ctx):

@@ -9,7 +9,7 @@ out=$root/gpurun_variants/$name.build
 mkdir -p $out
 flags="-gencode arch=compute_100a,code=sm_100a -std=c++17 -O3 -lineinfo -fmad=false -Xcompiler -fPIC $*"
 pids=""
-for w in 3 5 7 9 11 13 15; do
+for w in 1 3 5 7 9 11 13 15; do
   nvcc $flags -DNM03_K1_WINDOW=$w -Xptxas -v -c $pkg/csrc/nm03_k1_w.cu -o $out/k1_w$w.o 2> $out/k1_w$w.log & pids="$pids $!"
 done
 nvcc $flags -c $pkg/csrc/nm03_kernels.cu -o $out/kernels.o & pids="$pids $!"
