@@ -121,4 +121,39 @@ int nm03h_render_segmentation_grey(const void* lab, int lab_is_bits, int w, int 
   } catch (const std::exception&) { return -1; }
 }
 
+// CPU statement of nm03_outputs.export_blocks / export_nz: ImageRenderer's grey rendering of a 16-bit slice on a canvas
+// of its own size, then level shift, transform, quantisation and zigzag per 8x8 block (w, h multiples of 8)
+int nm03h_export_blocks_cpu(const void* px, int w, int h, int is_unsigned, int quality, int16_t* blocks, uint64_t* nz) {
+  try {
+    if (w <= 0 || h <= 0 || (w & 7) || (h & 7)) return -3;
+    auto img = nm03::Image::view(px, w, h, is_unsigned ? nm03::TYPE_UINT16 : nm03::TYPE_INT16);
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), w, h);
+    rti->connect(nm03::ImageRenderer::create()->addInputData(img));
+    rti->update();
+    const uint8_t* plane = rti->getOutputData<nm03::Image>(0)->greyPlane();
+    if (!plane) return -2;
+    const nm03::jpeg::Tables tb = nm03::jpeg::make_tables(quality);
+    size_t b = 0;
+    for (int by = 0; by < h; by += 8)
+      for (int bx = 0; bx < w; bx += 8, ++b)
+        nm03::jpeg::block_coefficients(plane + (size_t)by * w + bx, (size_t)w, tb.rq[0], blocks + 64 * b, nz + b);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
+// the reciprocal quantiser (64 floats, natural order) a caller hands to nm03_outputs.export_rq for a JPEG quality
+void nm03h_jpeg_rq(int quality, float* rq64) {
+  const nm03::jpeg::Tables tb = nm03::jpeg::make_tables(quality);
+  std::memcpy(rq64, tb.rq[0], 64 * sizeof(float));
+}
+
+long nm03h_jpeg_from_blocks(const int16_t* blocks, const uint64_t* nz, int w, int h, int quality, uint8_t* out, long cap) {
+  try {
+    const std::vector<uint8_t> b = nm03::jpeg::encode_blocks(blocks, nz, w, h, quality);
+    if ((long)b.size() > cap) return -(long)b.size();
+    std::memcpy(out, b.data(), b.size());
+    return (long)b.size();
+  } catch (const std::exception&) { return 0; }
+}
+
 }  // extern "C"

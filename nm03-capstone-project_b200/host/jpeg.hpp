@@ -221,33 +221,46 @@ inline void marker(std::vector<uint8_t>& o, uint8_t m, const std::vector<uint8_t
 
 }  // namespace detail
 
-// pixels: height*width*channels bytes, channels = 1 (grey) or 3 (RGB interleaved); quality 1..100.
-inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height, int channels, int quality = 90) {
+// Quantisation tables of a quality setting: q[t] = the table as stored in the file (t = 0 luma, 1 chroma; natural
+// order), rq[t] = reciprocal quantiser including the scaling of the AAN transform's outputs.
+struct Tables {
+  uint8_t q[2][64];
+  float rq[2][64];
+};
+inline Tables make_tables(int quality) {
   using namespace detail;
-  if (width <= 0 || height <= 0 || (channels != 1 && channels != 3)) throw std::runtime_error("jpeg: bad image");
+  Tables t;
   quality = quality < 1 ? 1 : (quality > 100 ? 100 : quality);
   const int scale = quality < 50 ? 5000 / quality : 200 - quality * 2;
-  uint8_t q[2][64];
   for (int i = 0; i < 64; ++i) {
     int a = (kQLuma[i] * scale + 50) / 100, b = (kQChroma[i] * scale + 50) / 100;
-    q[0][i] = (uint8_t)(a < 1 ? 1 : (a > 255 ? 255 : a));
-    q[1][i] = (uint8_t)(b < 1 ? 1 : (b > 255 ? 255 : b));
+    t.q[0][i] = (uint8_t)(a < 1 ? 1 : (a > 255 ? 255 : a));
+    t.q[1][i] = (uint8_t)(b < 1 ? 1 : (b > 255 ? 255 : b));
   }
-  float rq[2][64];  // reciprocal quantiser including the DCT's output scaling
   for (int i = 0; i < 64; ++i) {
     const float sc = 1.0f / (kAan[i >> 3] * kAan[i & 7] * 8.0f);
-    rq[0][i] = sc / q[0][i];
-    rq[1][i] = sc / q[1][i];
+    t.rq[0][i] = sc / t.q[0][i];
+    t.rq[1][i] = sc / t.q[1][i];
   }
-  static Huff hdc[2], hac[2];
-  static bool built = false;
-  if (!built) {
-    hdc[0].build(kDcLumaBits, kDcVals); hdc[1].build(kDcChromaBits, kDcVals);
-    hac[0].build(kAcLumaBits, kAcLumaVals); hac[1].build(kAcChromaBits, kAcChromaVals);
-    built = true;
+  return t;
+}
+
+namespace detail {
+
+struct HuffSet {
+  Huff dc[2], ac[2];
+  HuffSet() {
+    dc[0].build(kDcLumaBits, kDcVals); dc[1].build(kDcChromaBits, kDcVals);
+    ac[0].build(kAcLumaBits, kAcLumaVals); ac[1].build(kAcChromaBits, kAcChromaVals);
   }
-  std::vector<uint8_t> o;
-  o.reserve((size_t)width * height / 4 + 1024);
+};
+inline const HuffSet& huffman() {   // built once; initialisation of a function-local static is thread-safe
+  static const HuffSet hs;
+  return hs;
+}
+
+// SOI, APP0, DQT, SOF0, DHT and SOS of a baseline file
+inline void write_headers(std::vector<uint8_t>& o, int width, int height, int channels, const uint8_t (*q)[64]) {
   o.push_back(0xFF); o.push_back(0xD8);                                       // SOI
   marker(o, 0xE0, {'J', 'F', 'I', 'F', 0, 1, 1, 0, 0, 1, 0, 1, 0, 0});          // APP0
   for (int t = 0; t < (channels == 3 ? 2 : 1); ++t) {                          // DQT
@@ -277,13 +290,106 @@ inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height,
     p.push_back(0); p.push_back(63); p.push_back(0);
     marker(o, 0xDA, p);
   }
+}
+
+inline int bitsize(int v) { const unsigned a = (unsigned)(v < 0 ? -v : v); return a ? 32 - __builtin_clz(a) : 0; }
+
+// One block's symbols: the DC difference, then (run, size) symbols of the AC terms in zigzag order; code and value bits go
+// out together.  zz = the 64 quantised coefficients in zigzag order, nz = bit k set iff zz[k] != 0 (bit 0 is ignored).
+inline void put_block(BitWriter& bw, const Huff& hdc, const Huff& hac, const int16_t* zz, uint64_t nz, int& pred) {
+  const int diff = zz[0] - pred;
+  pred = zz[0];
+  {
+    const int sz = bitsize(diff);
+    const uint32_t vb = (uint32_t)(diff < 0 ? diff - 1 : diff) & ((1u << sz) - 1u);
+    bw.put(((uint32_t)hdc.code[sz] << sz) | vb, hdc.len[sz] + sz);
+  }
+  nz &= ~(uint64_t)1;
+  int prev = 0;
+  while (nz) {   // the map of the non-zero terms lets the loop jump from one to the next
+    const int i = __builtin_ctzll(nz);
+    nz &= nz - 1;
+    int run = i - prev - 1;
+    prev = i;
+    while (run > 15) { bw.put(hac.code[0xF0], hac.len[0xF0]); run -= 16; }
+    const int v = zz[i];
+    const int sz = bitsize(v), rs = (run << 4) | sz;
+    const uint32_t vb = (uint32_t)(v < 0 ? v - 1 : v) & ((1u << sz) - 1u);
+    bw.put(((uint32_t)hac.code[rs] << sz) | vb, hac.len[rs] + sz);
+  }
+  if (prev != 63) bw.put(hac.code[0x00], hac.len[0x00]);  // EOB
+}
+
+constexpr size_t kWorstBlock = 512;   // 64 coefficients x 26 bits, every byte stuffed, rounded up
+
+}  // namespace detail
+
+// A grey image whose blocks were transformed and quantised elsewhere (nm03_outputs.export_blocks: the GPU does it next to
+// the pipeline): zz = [blocks][64] quantised coefficients in zigzag order, blocks in raster order, nz = [blocks] maps of
+// the non-zero terms.  width and height are multiples of 8.  Produces the bytes encode() produces for the same image.
+inline std::vector<uint8_t> encode_blocks(const int16_t* zz, const uint64_t* nz, int width, int height, int quality = 90) {
+  using namespace detail;
+  if (width <= 0 || height <= 0 || (width & 7) || (height & 7)) throw std::runtime_error("jpeg: block input needs multiples of 8");
+  const Tables tb = make_tables(quality);
+  const HuffSet& hf = huffman();
+  std::vector<uint8_t> o;
+  o.reserve((size_t)width * height / 4 + 1024);
+  write_headers(o, width, height, 1, tb.q);
+  const int blocks_per_row = width / 8;
+  size_t pos = o.size();
+  int pred = 0;
+  BitWriter bw(nullptr);
+  size_t b = 0;
+  for (int by = 0; by < height; by += 8) {
+    if (o.size() - pos < (size_t)blocks_per_row * kWorstBlock + 64) o.resize(pos + (size_t)blocks_per_row * kWorstBlock * 2 + 64);
+    bw.p = o.data() + pos;
+    for (int bx = 0; bx < blocks_per_row; ++bx, ++b) put_block(bw, hf.dc[0], hf.ac[0], zz + 64 * b, nz[b], pred);
+    pos = (size_t)(bw.p - o.data());
+  }
+  if (o.size() - pos < 32) o.resize(pos + 32);
+  bw.p = o.data() + pos;
+  bw.flush();
+  pos = (size_t)(bw.p - o.data());
+  o.resize(pos);
+  o.push_back(0xFF); o.push_back(0xD9);  // EOI
+  return o;
+}
+
+// level shift, transform, quantisation and zigzag of one 8x8 block of a grey image, as encode() does them: the CPU
+// statement of what nm03_outputs.export_blocks holds (tests compare the two)
+inline void block_coefficients(const uint8_t* px, size_t stride, const float* rq, int16_t* zz, uint64_t* nz) {
+  using namespace detail;
+  int q[64];
+#if defined(__SSE2__)
+  quantise_sse2(px, stride, rq, q);
+#else
+  float blk[64];
+  for (int y = 0; y < 8; ++y) for (int x = 0; x < 8; ++x) blk[y * 8 + x] = (float)px[(size_t)y * stride + x] - 128.0f;
+  quantise_scalar(blk, rq, q);
+#endif
+  uint64_t m = 0;
+  for (int i = 0; i < 64; ++i) { zz[kUnzigzag[i]] = (int16_t)q[i]; }
+  for (int i = 0; i < 64; ++i) m |= (uint64_t)(zz[i] != 0) << i;
+  *nz = m;
+}
+
+// pixels: height*width*channels bytes, channels = 1 (grey) or 3 (RGB interleaved); quality 1..100.
+inline std::vector<uint8_t> encode(const uint8_t* pixels, int width, int height, int channels, int quality = 90) {
+  using namespace detail;
+  if (width <= 0 || height <= 0 || (channels != 1 && channels != 3)) throw std::runtime_error("jpeg: bad image");
+  const Tables tb = make_tables(quality);
+  const float (*rq)[64] = tb.rq;
+  const HuffSet& hf = huffman();
+  const Huff* hdc = hf.dc;
+  const Huff* hac = hf.ac;
+  std::vector<uint8_t> o;
+  o.reserve((size_t)width * height / 4 + 1024);
+  write_headers(o, width, height, channels, tb.q);
   // entropy-coded segment, written straight into the tail of `o` (grown by block row)
-  const size_t kWorstBlock = 512;         // 64 coefficients x 26 bits, every byte stuffed, rounded up
   const int blocks_per_row = ((width + 7) / 8) * channels;
   size_t pos = o.size();
   int pred[3] = {0, 0, 0};
   BitWriter bw(nullptr);
-  auto bitsize = [](int v) { const unsigned a = (unsigned)(v < 0 ? -v : v); return a ? 32 - __builtin_clz(a) : 0; };
   for (int by = 0; by < height; by += 8) {
     if (o.size() - pos < (size_t)blocks_per_row * kWorstBlock + 64) o.resize(pos + (size_t)blocks_per_row * kWorstBlock * 2 + 64);
     bw.p = o.data() + pos;

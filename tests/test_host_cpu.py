@@ -372,3 +372,33 @@ def test_segmentation_renderer_bit_planes(host, radius, shape):
     exp2[lab2 == 1] = 255
     exp2[interior2] = exp[interior].max() if interior.any() else 153
     np.testing.assert_array_equal(grey, exp2)
+
+
+# ---- blocks transformed elsewhere (nm03_outputs.export_blocks): the entropy coder alone gives the encoder's bytes ---------
+@pytest.mark.parametrize("unsigned", [0, 1])
+@pytest.mark.parametrize("shape,quality", [((512, 512), 75), ((64, 96), 90), ((128, 72), 30)])
+def test_jpeg_from_blocks_equals_direct_encoder(host, unsigned, shape, quality):
+    h, w = shape
+    host.nm03h_jpeg_from_blocks.restype = C.c_long
+    raw = cm.phantom(w, h, 3, 7, dtype=np.uint16 if unsigned else np.int16) if min(w, h) >= 100 else \
+        np.random.default_rng(w).integers(0, 3000, shape).astype(np.uint16 if unsigned else np.int16)
+    raw[:8, :16] = raw[0, 0]                                       # flat blocks: the direct encoder's DC-only shortcut
+    grey = np.zeros(shape, np.uint8)
+    assert host.nm03h_render_image_grey(raw.ctypes.data_as(C.c_void_p), w, h, unsigned, w, h, grey.ctypes.data_as(C.c_void_p)) == 0
+    direct = np.zeros(w * h * 2 + 4096, np.uint8)
+    n1 = host.nm03h_jpeg_encode(grey.ctypes.data_as(C.c_void_p), w, h, 1, quality, direct.ctypes.data_as(C.c_void_p), C.c_long(direct.size))
+    nb = (w // 8) * (h // 8)
+    blocks, nz = np.zeros((nb, 64), np.int16), np.zeros(nb, np.uint64)
+    assert host.nm03h_export_blocks_cpu(raw.ctypes.data_as(C.c_void_p), w, h, unsigned, quality,
+                                        blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p)) == 0
+    out = np.zeros(direct.size, np.uint8)
+    n2 = host.nm03h_jpeg_from_blocks(blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p), w, h, quality,
+                                     out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+    assert n1 > 0 and n1 == n2
+    np.testing.assert_array_equal(out[:n2], direct[:n1])
+    # the map of non-zero terms is what it says
+    np.testing.assert_array_equal(nz, (blocks != 0).astype(np.uint64) @ (np.uint64(1) << np.arange(64, dtype=np.uint64)))
+    # and the decoded image is the rendering, within JPEG's loss
+    from PIL import Image
+    dec = np.asarray(Image.open(io.BytesIO(out[:n2].tobytes())))
+    assert dec.shape == shape and np.abs(dec.astype(int) - grey.astype(int)).mean() < (8 if min(w, h) >= 100 else 45)   # noise images lose more
