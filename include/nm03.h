@@ -82,6 +82,18 @@ typedef struct nm03_outputs {
    * it is the form the segmentation kernel holds the mask in, and it crosses the host link at 1/8 of the bytes of
    * `dilated`.  May be requested with or without `dilated`. */
   uint32_t* dilated_bits;
+  /* Host export helper (no counterpart in the reference, whose renderers and JPEG writer live in FAST/Qt):
+   * the grey rendering of every INPUT slice — ImageRenderer's window/level on a canvas of the slice's own size,
+   * main_sequential.cpp:258-259 — level-shifted, transformed and quantised per 8x8 block for a baseline JPEG, so that the
+   * host is left with the entropy coding (host/jpeg.hpp encode_blocks gives the bytes of its own encode()).
+   * export_blocks: [n][(h/8)*(w/8)][64] quantised coefficients in zigzag order, blocks in raster order; export_nz:
+   * [n][(h/8)*(w/8)] 64-bit maps, bit k set iff coefficient k is non-zero; export_rq: 64 floats on the HOST (also for the
+   * _device variant), the reciprocal quantiser in natural order including the transform's scaling (jpeg::make_tables).
+   * All three or none; w and h must be multiples of 8 (NM03_ERR_UNSUPPORTED otherwise); not offered by
+   * nm03_process_batch_device_noalloc. */
+  int16_t* export_blocks;
+  uint64_t* export_nz;
+  const float* export_rq;
 } nm03_outputs;
 
 typedef struct nm03_ctx nm03_ctx;
@@ -92,7 +104,7 @@ typedef struct nm03_ctx nm03_ctx;
 int nm03_init(const int* gpu_ids, int n_gpus, nm03_ctx** out);
 void nm03_shutdown(nm03_ctx* ctx);
 const char* nm03_last_error(void);
-int nm03_version(void);
+int nm03_version(void);   /* 102: nm03_outputs.export_* */
 int nm03_gpu_count(const nm03_ctx* ctx);
 /* Number of CUDA devices visible to the process (0 if none); lets a driver build the gpu_ids list for
  * nm03_init.  No counterpart in the reference, which uses whatever single device FAST picks. */

@@ -51,6 +51,7 @@ class Outputs(C.Structure):
         ("dilated", C.c_void_p), ("eroded", C.c_void_p), ("rg_mask", C.c_void_p),
         ("sharpened", C.c_void_p), ("median", C.c_void_p), ("rg_iterations", C.c_void_p),
         ("dilated_bits", C.c_void_p),
+        ("export_blocks", C.c_void_p), ("export_nz", C.c_void_p), ("export_rq", C.c_void_p),
     ]
 
 
@@ -204,6 +205,18 @@ class Context:
     def _host_outputs(n, h, w, want, res):
         o = Outputs()
         for name in want:
+            if name in ("export", "export_rq"):   # res["export_rq"]: 64 float32 from the caller (jpeg::make_tables / nm03h_jpeg_rq)
+                if o.export_rq:
+                    continue
+                nb = (h // 8) * (w // 8)
+                res["export_rq"] = np.ascontiguousarray(res["export_rq"], np.float32)
+                res.setdefault("export_blocks", np.empty((n, nb, 64), np.int16))
+                res.setdefault("export_nz", np.empty((n, nb), np.uint64))
+                for k in ("export_blocks", "export_nz", "export_rq"):
+                    setattr(o, k, res[k].ctypes.data)
+                continue
+            if name in ("export_blocks", "export_nz"):
+                continue
             if name not in res:
                 if name in ("sharpened", "median"):
                     res[name] = np.empty((n, h, w), np.float32)

@@ -6,6 +6,7 @@
 // slots make the context re-entrant without any global lock on the data path.
 #include "../../include/nm03.h"
 #include "nm03_device.h"
+#include "nm03_export.h"
 
 #include <atomic>
 #include <cmath>
@@ -85,6 +86,8 @@ struct Slot {
   size_t lut_bytes = 0;
   void* bigmed = nullptr;         // scratch: raw-sample median plane [n][h][w] of windows above 15x15 (two-pass path)
   size_t bigmed_bytes = 0;
+  void* win = nullptr;            // scratch: [n] (min, max) of each slice, the rendering window of nm03_outputs.export_blocks
+  size_t win_bytes = 0;
   float lut_key[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool lut_valid = false;
   bool busy = false;
@@ -556,6 +559,31 @@ int run_segment(Worker* wk, Slot* s, cudaStream_t st, const nm03::SegParams& seg
 }
 
 // make sure the slot's f(key) table matches these parameters (rebuilt by a tiny kernel when they change)
+// nm03_outputs.export_*: all three pointers or none, whole 8x8 blocks only
+int check_export(const nm03_outputs* o, int w, int h) {
+  if (!o->export_blocks && !o->export_nz && !o->export_rq) return NM03_OK;
+  if (!o->export_blocks || !o->export_nz || !o->export_rq)
+    return fail(NM03_ERR_INVALID, "export_blocks, export_nz and export_rq go together");
+  if ((w & 7) || (h & 7))
+    return fail(NM03_ERR_UNSUPPORTED, "export blocks need a width and height that are multiples of 8, got %dx%d", w, h);
+  return NM03_OK;
+}
+
+// the export half of a batch (see nm03_export.h): queued behind the pipeline on the same stream, reads the same input
+int enqueue_export(Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h, int input_unsigned, const nm03_outputs* d_out) {
+  if (!d_out->export_blocks) return NM03_OK;
+  int rc;
+  if ((rc = ensure(s, &s->win, &s->win_bytes, (size_t)n * sizeof(int2)))) return rc;
+  nm03::ExportParams e;
+  e.in = d_slices; e.n = n; e.w = w; e.h = h; e.input_unsigned = input_unsigned;
+  e.mm = (int2*)s->win;
+  e.blocks = d_out->export_blocks;
+  e.nz = (unsigned long long*)d_out->export_nz;
+  memcpy(e.rq, d_out->export_rq, sizeof(e.rq));
+  CK(nm03::launch_export_blocks(e, st));
+  return NM03_OK;
+}
+
 // K1 for any supported window.  Up to 15x15 the fused kernel does everything; above, the window median of the raw
 // samples is taken first (generic kernel, slot scratch) and K1 runs on that plane with the 1x1 window.  The caller has
 // ordered the stream after the slot's previous use.
@@ -600,6 +628,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
                      const nm03_params* p, const int* seeds_xy, int n_seeds, const nm03_outputs* d_out, SegPolicy policy) {
   int rc, hs = 0;
   if ((rc = check_params(p, w, h, true))) return rc;
+  if ((rc = check_export(d_out, w, h))) return rc;
   const bool exact = d_out->sharpened || g_force_exact, erode_out = p->erode_size > 0 && d_out->eroded;
   nm03::PreParams pre;
   nm03::SegParams seg;
@@ -668,6 +697,7 @@ int enqueue_pipeline(Worker* wk, Slot* s, cudaStream_t st, const void* d_slices,
   seg.rg_mask = d_out->rg_mask;
   seg.iterations = d_out->rg_iterations;
   if ((rc = run_segment(wk, s, st, seg))) return rc;
+  if ((rc = enqueue_export(s, st, d_slices, n, w, h, pre.input_unsigned, d_out))) return rc;
   if (prof) {
     CK(cudaEventRecord(rec.e[2], st));
     std::lock_guard<std::mutex> lk(wk->prof_mu);
@@ -726,6 +756,8 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
   if (n == 0) return NM03_OK;
   if ((rc = check_params(params, w, h, true))) return rc;
   if ((rc = check_preprocess(params, &hs))) return rc;
+  if (d_out->export_blocks || d_out->export_nz || d_out->export_rq)
+    return fail(NM03_ERR_UNSUPPORTED, "export blocks need scratch memory and are only available through nm03_process_batch_device");
   if (params->median_window > nm03::K1_MAX_WINDOW)
     return fail(NM03_ERR_UNSUPPORTED, "median windows above %d need scratch memory for a second pass and are only available through "
                 "nm03_process_batch_device, got %d", nm03::K1_MAX_WINDOW, params->median_window);
@@ -772,7 +804,7 @@ int nm03_process_batch_device_noalloc(nm03_ctx* ctx, int gpu, const void* d_slic
 }
 
 const char* nm03_last_error(void) { return g_err; }
-int nm03_version(void) { return 101; }   // 101: nm03_outputs.dilated_bits, async tickets
+int nm03_version(void) { return 102; }   // 101: nm03_outputs.dilated_bits, async tickets; 102: nm03_outputs.export_*
 
 void nm03_default_params(nm03_params* p) {
   if (!p) return;
@@ -866,6 +898,7 @@ void nm03_shutdown(nm03_ctx* ctx) {
       if (s.stage_out) cudaFree(s.stage_out);
       if (s.lut) cudaFree(s.lut);
       if (s.bigmed) cudaFree(s.bigmed);
+      if (s.win) cudaFree(s.win);
       if (s.sched) cudaFree(s.sched);
       if (s.gmask) cudaFree(s.gmask);
       if (s.dflag) cudaFree(s.dflag);
@@ -1007,6 +1040,7 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
     if (o.median) o.median += start * npx;
     if (o.rg_iterations) o.rg_iterations += start;
     if (o.dilated_bits) o.dilated_bits += start * h * wpr;
+    if (o.export_blocks) { o.export_blocks += (size_t)start * (w / 8) * (h / 8) * 64; o.export_nz += (size_t)start * (w / 8) * (h / 8); }
     rc = NM03_OK;
     if (ss != st) {
       cudaError_t e = cudaStreamWaitEvent(ss, lease.s->fork, 0);
@@ -1042,13 +1076,18 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
   const size_t o_med = out_bytes; if (out->median) out_bytes += cnt * npx * 4;
   const size_t o_bits = out_bytes; if (out->dilated_bits) out_bytes += (size_t)cnt * h * wpr * 4;
   const size_t o_it = out_bytes; if (out->rg_iterations) out_bytes += (size_t)cnt * 4;
+  const size_t nblk = (size_t)(w / 8) * (h / 8);   // export blocks: 128 bytes of coefficients + an 8-byte map each
+  out_bytes = (out_bytes + 15) & ~(size_t)15;
+  const size_t o_blk = out_bytes; if (out->export_blocks) out_bytes += (size_t)cnt * nblk * 128;
+  const size_t o_nz = out_bytes; if (out->export_blocks) out_bytes += (size_t)cnt * nblk * 8;
   // staging is sized for the whole batch even when the call works in chunks: the next batch of this shape may
   // come unchunked, and growing a buffer then would put a cudaFree/cudaMalloc in its path
   const size_t per_slice = npx * ((out->dilated ? 1 : 0) + (out->eroded ? 1 : 0) + (out->rg_mask ? 1 : 0) +
                                   (out->sharpened ? 4 : 0) + (out->median ? 4 : 0)) + (out->dilated_bits ? h * wpr * 4 : 0) +
-                           (out->rg_iterations ? 4 : 0);
+                           (out->rg_iterations ? 4 : 0) + (out->export_blocks ? nblk * 136 : 0);
+  if ((rc = check_export(out, w, h))) return rc;
   if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, (size_t)n_total * npx * 2))) return rc;
-  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n_total * per_slice + 32)))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n_total * per_slice + 64)))) return rc;
   cudaStream_t st = s->stream;
   cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
                                   cudaMemcpyHostToDevice, st);
@@ -1062,6 +1101,7 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
   if (out->median) d.median = (float*)(so + o_med);
   if (out->dilated_bits) d.dilated_bits = (uint32_t*)(so + o_bits);
   if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
+  if (out->export_blocks) { d.export_blocks = (int16_t*)(so + o_blk); d.export_nz = (uint64_t*)(so + o_nz); d.export_rq = out->export_rq; }
   // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
   if ((rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, SEG_LATENCY))) return rc;
 #define NM03_D2H(field, off, elem)                                                                          \
@@ -1078,6 +1118,10 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
     e = cudaMemcpyAsync(out->dilated_bits + (size_t)start * h * wpr, so + o_bits, (size_t)cnt * h * wpr * 4, cudaMemcpyDeviceToHost, st);
   if (out->rg_iterations && e == cudaSuccess)
     e = cudaMemcpyAsync(out->rg_iterations + start, so + o_it, (size_t)cnt * 4, cudaMemcpyDeviceToHost, st);
+  if (out->export_blocks && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->export_blocks + (size_t)start * nblk * 64, so + o_blk, (size_t)cnt * nblk * 128, cudaMemcpyDeviceToHost, st);
+  if (out->export_blocks && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->export_nz + (size_t)start * nblk, so + o_nz, (size_t)cnt * nblk * 8, cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
   if (e != cudaSuccess) return fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e));
   return NM03_OK;

@@ -44,6 +44,7 @@ struct Options {
   std::vector<int> gpus;
   int batch = 25, streams = 0, host_threads = 0;   // feeders per GPU, 0 = choose (see runBatch)
   bool do_export = true, dump_masks = false, lowcontrast = false;
+  bool cpu_dct = false;      // --cpu-dct: render, transform and quantise the original on the host (default: the GPU does, next to the pipeline)
   bool byte_masks = false;   // --byte-masks: fetch the uint8 mask from the GPU instead of the bit-packed one (8x the bytes over the link)
   int patients = 20, slices = 24, size = 512;
 };
@@ -237,7 +238,10 @@ struct BufRing {
 };
 
 // mask: uint8 labels, or (bits = true) the bit-packed words of nm03_outputs.dilated_bits
-void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const void* mask, bool bits, int w, int h) {
+// blocks / nz: the original's quantised 8x8 blocks from the GPU (nm03_outputs.export_blocks), or null: rendered and
+// transformed here
+void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const void* mask, bool bits, int w, int h,
+                 const int16_t* blocks = nullptr, const uint64_t* nz = nullptr) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
   // views of the pinned staging buffers (they outlive this call): no copies, and the segmentation renderer works on the
@@ -247,9 +251,20 @@ void exportSlice(const fs::path& dir, const std::string& file, const int16_t* ra
   LabelColors colors;
   colors[1] = Color::White();
   auto rti = RenderToImage::create(Color::Black(), 512, 512);  // main_sequential.cpp:258
-  rti->connect(ImageRenderer::create()->addInputData(orig));
-  rti->update();
-  ImageFileExporter::create((dir / (stem + "_original.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
+  if (blocks && w == 512 && h == 512) {
+    // the canvas is the slice's own size, so the GPU's blocks are the rendering's: only the entropy coding is left
+    const std::vector<uint8_t> b = jpeg::encode_blocks(blocks, nz, w, h, ImageFileExporter::kDefaultJpegQuality);
+    const std::string path = (dir / (stem + "_original.jpg")).string();
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) throw Exception("cannot write " + path);
+    const size_t nw = std::fwrite(b.data(), 1, b.size(), f);
+    std::fclose(f);
+    if (nw != b.size()) throw Exception("short write " + path);
+  } else {
+    rti->connect(ImageRenderer::create()->addInputData(orig));
+    rti->update();
+    ImageFileExporter::create((dir / (stem + "_original.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
+  }
   rti->removeAllRenderers();
   rti->connect(SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->addInputData(seg));
   rti->update();
@@ -334,10 +349,20 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
                                                                  slices[first].rescale_intercept) == 0;
     // the mask comes back bit-packed (1/8 of the bytes over the host link) and is unpacked by the worker that needs it
     const size_t wpr = (size_t)(w + 31) / 32, mask_bytes = opt.byte_masks ? npx : h * wpr * 4;
-    out.reserve(m * mask_bytes);
+    // with export on 512x512 slices (the canvas size of the two renders) the GPU also hands back the original's
+    // quantised JPEG blocks: 128 bytes of coefficients + an 8-byte map per 8x8 block, behind the masks
+    const bool gpu_blocks = opt.do_export && !opt.cpu_dct && w == 512 && h == 512;
+    const size_t nblk = (size_t)(w / 8) * (h / 8), masks_end = (m * mask_bytes + 63) & ~(size_t)63;
+    out.reserve(masks_end + (gpu_blocks ? m * nblk * 136 : 0));
     nm03_outputs o = {};
     if (opt.byte_masks) o.dilated = (uint8_t*)out.p;
     else o.dilated_bits = (uint32_t*)out.p;
+    static const nm03::jpeg::Tables tables = nm03::jpeg::make_tables(nm03::ImageFileExporter::kDefaultJpegQuality);
+    if (gpu_blocks) {
+      o.export_blocks = (int16_t*)((uint8_t*)out.p + masks_end);
+      o.export_nz = (uint64_t*)((uint8_t*)out.p + masks_end + m * nblk * 128);
+      o.export_rq = tables.rq[0];
+    }
     std::vector<int> status(m, 0);
     const int rc = nm03_process_batch(ctx, gpu, in.p, m, w, h, &params, nullptr, 0, &o, status.data());
     timer.lap(tot.ns_gpu);
@@ -370,6 +395,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       const void* in_p = in.p;
       const void* out_p = out.p;
       const bool is_unsigned = params.input_unsigned != 0, byte_masks = opt.byte_masks;
+      const int16_t* blk_p = o.export_blocks;
+      const uint64_t* nz_p = o.export_nz;
       Totals* totp = &tot;
       BufRing* ringp = &ring;
       Pool* pool = g_pool;
@@ -378,7 +405,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
         const auto t0 = Clock::now();
         try {
           exportSlice(outdir, names[j], (const int16_t*)((const uint8_t*)in_p + j * npx * 2), is_unsigned,
-                      (const uint8_t*)out_p + j * mask_bytes, !byte_masks, w, h);
+                      (const uint8_t*)out_p + j * mask_bytes, !byte_masks, w, h, blk_p ? blk_p + j * nblk * 64 : nullptr,
+                      nz_p ? nz_p + j * nblk : nullptr);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(totp->log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -390,7 +418,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       for (int j = 0; j < m; ++j) {
         try {
           exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
-                      (const uint8_t*)out.p + j * mask_bytes, !opt.byte_masks, w, h);
+                      (const uint8_t*)out.p + j * mask_bytes, !opt.byte_masks, w, h,
+                      o.export_blocks ? o.export_blocks + j * nblk * 64 : nullptr, o.export_nz ? o.export_nz + j * nblk : nullptr);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(tot.log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -441,7 +470,9 @@ int runBatch(Options opt) {
     for (int b = 0; b < (opt.do_export && !sequential ? 3 : 1); ++b) {
       rings.back()->sets.emplace_back(new BufSet());
       rings.back()->sets.back()->in.reserve((size_t)opt.batch * 512 * 512 * 2);
-      rings.back()->sets.back()->out.reserve((size_t)opt.batch * 512 * 512);
+      // masks (at most a byte per pixel) and, with export, the original's JPEG blocks from the GPU (136 bytes per 8x8 block)
+      rings.back()->sets.back()->out.reserve((size_t)opt.batch * 512 * 512 + 64 +
+                                             (opt.do_export && !opt.cpu_dct ? (size_t)opt.batch * 4096 * 136 : 0));
     }
   }
   for (int g = 0; g < n_gpus_used; ++g) {
@@ -453,6 +484,12 @@ int runBatch(Options opt) {
     nm03_default_params(&params);
     nm03_outputs o = {};
     o.dilated = (uint8_t*)out.p;
+    static const nm03::jpeg::Tables warm_tables = nm03::jpeg::make_tables(nm03::ImageFileExporter::kDefaultJpegQuality);
+    if (opt.do_export && !opt.cpu_dct) {   // as the feeders will ask for it, so that the staging is sized and the kernels are loaded
+      o.export_blocks = (int16_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64);
+      o.export_nz = (uint64_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 128);
+      o.export_rq = warm_tables.rq[0];
+    }
     if (nm03_process_batch(ctx, g, in.p, m, 512, 512, &params, nullptr, 0, &o, nullptr) != NM03_OK) {
       std::cerr << "Fatal error: " << nm03_last_error() << std::endl;
       nm03_shutdown(ctx);
@@ -594,6 +631,7 @@ int main(int argc, char** argv) {
     else if (a == "--no-export") opt.do_export = false;
     else if (a == "--dump-masks") opt.dump_masks = true;
     else if (a == "--byte-masks") opt.byte_masks = true;
+    else if (a == "--cpu-dct") opt.cpu_dct = true;
     else if (a == "--test-pipeline") opt.test_file = val();
     else if (a == "--make-dataset") opt.make_dataset = val();
     else if (a == "--patients") opt.patients = std::atoi(val().c_str());
