@@ -68,6 +68,13 @@ typedef struct nm03_params {
   int input_unsigned;                            /* 0 = int16 pixels, 1 = uint16 pixels */
 } nm03_params;
 
+/* Greys and border radius of the result's rendering for nm03_outputs.export_seg_blocks: SegmentationRenderer::create(
+ * labelColors, 0.6f, 1.0f, 2) over black (main_sequential.cpp:261) gives background 0, interior 153, border 255, radius 2. */
+typedef struct nm03_export_style {
+  uint8_t background, interior, border;
+  int border_radius;                             /* 0..7 */
+} nm03_export_style;
+
 /* Optional per-slice outputs of nm03_process_batch*; any pointer may be NULL.  Each is a dense
  * [n][h][w] array (host pointers for nm03_process_batch, device pointers for the _device variant). */
 typedef struct nm03_outputs {
@@ -94,6 +101,12 @@ typedef struct nm03_outputs {
   int16_t* export_blocks;
   uint64_t* export_nz;
   const float* export_rq;
+  /* The same for the rendering of the RESULT (SegmentationRenderer of the dilated mask on a canvas of the slice's own
+   * size, main_sequential.cpp:261-262): blocks and maps laid out as above, quantised with export_rq; export_seg_style (on
+   * the HOST) holds the three greys and the border radius.  Needs dilated_bits, export_rq, export_seg_nz and the style. */
+  int16_t* export_seg_blocks;
+  uint64_t* export_seg_nz;
+  const nm03_export_style* export_seg_style;
 } nm03_outputs;
 
 typedef struct nm03_ctx nm03_ctx;

@@ -52,7 +52,13 @@ class Outputs(C.Structure):
         ("sharpened", C.c_void_p), ("median", C.c_void_p), ("rg_iterations", C.c_void_p),
         ("dilated_bits", C.c_void_p),
         ("export_blocks", C.c_void_p), ("export_nz", C.c_void_p), ("export_rq", C.c_void_p),
+        ("export_seg_blocks", C.c_void_p), ("export_seg_nz", C.c_void_p), ("export_seg_style", C.c_void_p),
     ]
+
+
+class ExportStyle(C.Structure):
+    """nm03_export_style (include/nm03.h)."""
+    _fields_ = [("background", C.c_uint8), ("interior", C.c_uint8), ("border", C.c_uint8), ("border_radius", C.c_int)]
 
 
 class Nm03Error(RuntimeError):
@@ -214,8 +220,14 @@ class Context:
                 res.setdefault("export_nz", np.empty((n, nb), np.uint64))
                 for k in ("export_blocks", "export_nz", "export_rq"):
                     setattr(o, k, res[k].ctypes.data)
+                if "export_seg_style" in res:   # an ExportStyle: also the rendering of the result (needs "dilated_bits" in want)
+                    res.setdefault("export_seg_blocks", np.empty((n, nb, 64), np.int16))
+                    res.setdefault("export_seg_nz", np.empty((n, nb), np.uint64))
+                    o.export_seg_blocks = res["export_seg_blocks"].ctypes.data
+                    o.export_seg_nz = res["export_seg_nz"].ctypes.data
+                    o.export_seg_style = C.addressof(res["export_seg_style"])
                 continue
-            if name in ("export_blocks", "export_nz"):
+            if name in ("export_blocks", "export_nz", "export_seg_blocks", "export_seg_nz", "export_seg_style"):
                 continue
             if name not in res:
                 if name in ("sharpened", "median"):

@@ -561,11 +561,21 @@ int run_segment(Worker* wk, Slot* s, cudaStream_t st, const nm03::SegParams& seg
 // make sure the slot's f(key) table matches these parameters (rebuilt by a tiny kernel when they change)
 // nm03_outputs.export_*: all three pointers or none, whole 8x8 blocks only
 int check_export(const nm03_outputs* o, int w, int h) {
-  if (!o->export_blocks && !o->export_nz && !o->export_rq) return NM03_OK;
+  if (!o->export_blocks && !o->export_nz && !o->export_rq) {
+    if (o->export_seg_blocks || o->export_seg_nz || o->export_seg_style)
+      return fail(NM03_ERR_INVALID, "export_seg_blocks is only offered together with export_blocks");
+    return NM03_OK;
+  }
   if (!o->export_blocks || !o->export_nz || !o->export_rq)
     return fail(NM03_ERR_INVALID, "export_blocks, export_nz and export_rq go together");
   if ((w & 7) || (h & 7))
     return fail(NM03_ERR_UNSUPPORTED, "export blocks need a width and height that are multiples of 8, got %dx%d", w, h);
+  if (o->export_seg_blocks || o->export_seg_nz || o->export_seg_style) {
+    if (!o->export_seg_blocks || !o->export_seg_nz || !o->export_seg_style || !o->dilated_bits)
+      return fail(NM03_ERR_INVALID, "export_seg_blocks needs export_seg_nz, export_seg_style and dilated_bits");
+    if (o->export_seg_style->border_radius < 0 || o->export_seg_style->border_radius > 7)
+      return fail(NM03_ERR_UNSUPPORTED, "export border radius %d not implemented (0..7 are)", o->export_seg_style->border_radius);
+  }
   return NM03_OK;
 }
 
@@ -581,6 +591,23 @@ int enqueue_export(Slot* s, cudaStream_t st, const void* d_slices, int n, int w,
   e.nz = (unsigned long long*)d_out->export_nz;
   memcpy(e.rq, d_out->export_rq, sizeof(e.rq));
   CK(nm03::launch_export_blocks(e, st));
+  if (d_out->export_seg_blocks) {
+    nm03::ExportSegParams g;
+    g.bits = d_out->dilated_bits; g.n = n; g.w = w; g.h = h; g.wpr = (w + 31) / 32;
+    const nm03_export_style& sty = *d_out->export_seg_style;
+    g.radius = sty.border_radius;
+    memset(g.hw, 0, sizeof(g.hw));
+    for (int b = -g.radius; b <= g.radius; ++b) {   // disc: offsets with a*a + b*b <= R*R (SegmentationRenderer, host/nm03.hpp)
+      int a = 0;
+      while ((a + 1) * (a + 1) + b * b <= g.radius * g.radius) ++a;
+      g.hw[b + g.radius] = (int8_t)a;
+    }
+    g.background = sty.background; g.interior = sty.interior; g.border = sty.border;
+    g.blocks = d_out->export_seg_blocks;
+    g.nz = (unsigned long long*)d_out->export_seg_nz;
+    memcpy(g.rq, d_out->export_rq, sizeof(g.rq));
+    CK(nm03::launch_export_seg_blocks(g, st));
+  }
   return NM03_OK;
 }
 
@@ -1041,6 +1068,7 @@ int nm03_process_batch_device(nm03_ctx* ctx, int gpu, const void* d_slices, int 
     if (o.rg_iterations) o.rg_iterations += start;
     if (o.dilated_bits) o.dilated_bits += start * h * wpr;
     if (o.export_blocks) { o.export_blocks += (size_t)start * (w / 8) * (h / 8) * 64; o.export_nz += (size_t)start * (w / 8) * (h / 8); }
+    if (o.export_seg_blocks) { o.export_seg_blocks += (size_t)start * (w / 8) * (h / 8) * 64; o.export_seg_nz += (size_t)start * (w / 8) * (h / 8); }
     rc = NM03_OK;
     if (ss != st) {
       cudaError_t e = cudaStreamWaitEvent(ss, lease.s->fork, 0);
@@ -1080,14 +1108,18 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
   out_bytes = (out_bytes + 15) & ~(size_t)15;
   const size_t o_blk = out_bytes; if (out->export_blocks) out_bytes += (size_t)cnt * nblk * 128;
   const size_t o_nz = out_bytes; if (out->export_blocks) out_bytes += (size_t)cnt * nblk * 8;
+  out_bytes = (out_bytes + 15) & ~(size_t)15;   // the block kernels store 16 bytes at a time
+  const size_t o_sblk = out_bytes; if (out->export_seg_blocks) out_bytes += (size_t)cnt * nblk * 128;
+  const size_t o_snz = out_bytes; if (out->export_seg_blocks) out_bytes += (size_t)cnt * nblk * 8;
   // staging is sized for the whole batch even when the call works in chunks: the next batch of this shape may
   // come unchunked, and growing a buffer then would put a cudaFree/cudaMalloc in its path
   const size_t per_slice = npx * ((out->dilated ? 1 : 0) + (out->eroded ? 1 : 0) + (out->rg_mask ? 1 : 0) +
                                   (out->sharpened ? 4 : 0) + (out->median ? 4 : 0)) + (out->dilated_bits ? h * wpr * 4 : 0) +
-                           (out->rg_iterations ? 4 : 0) + (out->export_blocks ? nblk * 136 : 0);
+                           (out->rg_iterations ? 4 : 0) + (out->export_blocks ? nblk * 136 : 0) +
+                           (out->export_seg_blocks ? nblk * 136 : 0);
   if ((rc = check_export(out, w, h))) return rc;
   if ((rc = ensure(s, &s->stage_in, &s->stage_in_bytes, (size_t)n_total * npx * 2))) return rc;
-  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n_total * per_slice + 64)))) return rc;
+  if ((rc = ensure(s, &s->stage_out, &s->stage_out_bytes, std::max(out_bytes, (size_t)n_total * per_slice + 96)))) return rc;
   cudaStream_t st = s->stream;
   cudaError_t e = cudaMemcpyAsync(s->stage_in, (const uint8_t*)slices + (size_t)start * npx * 2, cnt * npx * 2,
                                   cudaMemcpyHostToDevice, st);
@@ -1102,6 +1134,9 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
   if (out->dilated_bits) d.dilated_bits = (uint32_t*)(so + o_bits);
   if (out->rg_iterations) d.rg_iterations = (int32_t*)(so + o_it);
   if (out->export_blocks) { d.export_blocks = (int16_t*)(so + o_blk); d.export_nz = (uint64_t*)(so + o_nz); d.export_rq = out->export_rq; }
+  if (out->export_seg_blocks) {
+    d.export_seg_blocks = (int16_t*)(so + o_sblk); d.export_seg_nz = (uint64_t*)(so + o_snz); d.export_seg_style = out->export_seg_style;
+  }
   // (host path: the other slots mostly hold copies in flight, and the chunk's latency is on the call's critical path)
   if ((rc = enqueue_pipeline(wk, s, st, s->stage_in, cnt, w, h, params, seeds_xy, n_seeds, &d, SEG_LATENCY))) return rc;
 #define NM03_D2H(field, off, elem)                                                                          \
@@ -1122,6 +1157,10 @@ static int enqueue_host_chunk(Worker* wk, Slot* s, const void* slices, int start
     e = cudaMemcpyAsync(out->export_blocks + (size_t)start * nblk * 64, so + o_blk, (size_t)cnt * nblk * 128, cudaMemcpyDeviceToHost, st);
   if (out->export_blocks && e == cudaSuccess)
     e = cudaMemcpyAsync(out->export_nz + (size_t)start * nblk, so + o_nz, (size_t)cnt * nblk * 8, cudaMemcpyDeviceToHost, st);
+  if (out->export_seg_blocks && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->export_seg_blocks + (size_t)start * nblk * 64, so + o_sblk, (size_t)cnt * nblk * 128, cudaMemcpyDeviceToHost, st);
+  if (out->export_seg_blocks && e == cudaSuccess)
+    e = cudaMemcpyAsync(out->export_seg_nz + (size_t)start * nblk, so + o_snz, (size_t)cnt * nblk * 8, cudaMemcpyDeviceToHost, st);
   if (e == cudaSuccess) e = cudaEventRecord(s->done, st);
   if (e != cudaSuccess) return fail(NM03_ERR_CUDA, "D2H copy failed: %s", cudaGetErrorString(e));
   return NM03_OK;

@@ -75,6 +75,31 @@ __device__ constexpr unsigned char kZig[64] = {0,  1,  8,  16, 9,  2,  3,  10, 1
                                                41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
                                                30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
+// forward transform (rows, then columns), quantisation (round half away from zero) and zigzag of one level-shifted block;
+// two coefficients per stored word
+__device__ __forceinline__ void transform_quantise_store(float (&d)[8][8], const float* __restrict__ rq, int16_t* __restrict__ blocks,
+                                                         unsigned long long* __restrict__ nzp) {
+#pragma unroll
+  for (int y = 0; y < 8; ++y) aan8(d[y][0], d[y][1], d[y][2], d[y][3], d[y][4], d[y][5], d[y][6], d[y][7]);   // rows
+#pragma unroll
+  for (int x = 0; x < 8; ++x) aan8(d[0][x], d[1][x], d[2][x], d[3][x], d[4][x], d[5][x], d[6][x], d[7][x]);   // columns
+  unsigned long long nz = 0ull;
+  uint32_t wout[32];
+#pragma unroll
+  for (int k = 0; k < 64; ++k) {
+    const int i = kZig[k];
+    const float qv = __fmul_rn(d[i >> 3][i & 7], rq[i]);
+    const int c = __float2int_rz(__fadd_rn(qv, copysignf(0.5f, qv)));
+    if (c != 0) nz |= 1ull << k;
+    if (k & 1) wout[k >> 1] |= (uint32_t)(c & 0xffff) << 16;
+    else wout[k >> 1] = (uint32_t)(c & 0xffff);
+  }
+  uint4* dst = reinterpret_cast<uint4*>(blocks);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) dst[k] = make_uint4(wout[4 * k], wout[4 * k + 1], wout[4 * k + 2], wout[4 * k + 3]);
+  *nzp = nz;
+}
+
 constexpr int kExportThreads = 128;
 
 __global__ void __launch_bounds__(kExportThreads) k_render_dct(const __grid_constant__ ExportParams p) {
@@ -103,26 +128,51 @@ __global__ void __launch_bounds__(kExportThreads) k_render_dct(const __grid_cons
       d[y][x] = __fsub_rn((float)grey, 128.0f);                   // level shift
     }
   }
+  transform_quantise_store(d, p.rq, p.blocks + (size_t)b * 64, p.nz + b);
+}
+
+// 32 mask pixels of row y starting at pixel x0 - 8 (x0 a multiple of 8); pixels outside the image are 0
+__device__ __forceinline__ uint32_t mask_window(const uint32_t* __restrict__ plane, int y, int h, int wpr, int x0) {
+  if (y < 0 || y >= h) return 0u;
+  const uint32_t* __restrict__ row = plane + (size_t)y * wpr;
+  const int k = x0 >> 5, s = 24 + (x0 & 31);                    // start within the string (word k-1, word k, word k+1)
+  const unsigned long long lo = k > 0 ? __ldg(row + k - 1) : 0u, mid = __ldg(row + k), hi = k + 1 < wpr ? __ldg(row + k + 1) : 0u;
+  return s < 32 ? (uint32_t)((lo | (mid << 32)) >> s) : (uint32_t)((mid | (hi << 32)) >> (s - 32));
+}
+
+__global__ void __launch_bounds__(kExportThreads) k_seg_render_dct(const __grid_constant__ ExportSegParams p) {
+  const int bw = p.w >> 3, nb = bw * (p.h >> 3);
+  const long long b = (long long)blockIdx.x * kExportThreads + threadIdx.x;
+  if (b >= (long long)p.n * nb) return;
+  const int slice = (int)(b / nb), bi = (int)(b - (long long)slice * nb);
+  const int by = bi / bw, bx = bi - by * bw;
+  const uint32_t* __restrict__ plane = p.bits + (size_t)slice * p.h * p.wpr;
+  const int R = p.radius, x0 = 8 * bx, y0 = 8 * by;
+  // rows y0-R .. y0+7+R of the mask around the block; bit 8+j of a window = pixel x0+j
+  uint32_t win[8 + 14];
 #pragma unroll
-  for (int y = 0; y < 8; ++y) aan8(d[y][0], d[y][1], d[y][2], d[y][3], d[y][4], d[y][5], d[y][6], d[y][7]);   // rows
+  for (int r = 0; r < 8 + 14; ++r) win[r] = r < 8 + 2 * R ? mask_window(plane, y0 - R + r, p.h, p.wpr, x0) : 0u;
+  float d[8][8];
 #pragma unroll
-  for (int x = 0; x < 8; ++x) aan8(d[0][x], d[1][x], d[2][x], d[3][x], d[4][x], d[5][x], d[6][x], d[7][x]);   // columns
-  // quantise (round half away from zero), in zigzag order, two coefficients per word
-  unsigned long long nz = 0ull;
-  uint32_t wout[32];
+  for (int y = 0; y < 8; ++y) {
+    const uint32_t m = win[y + R];
+    // interior = the mask eroded by the border disc: row offset b contributes the row eroded horizontally by hw[b]
+    uint32_t interior = m;
+    for (int bb = -R; bb <= R && interior; ++bb) {
+      const uint32_t rw = win[y + R + bb];
+      uint32_t e = rw;
+      const int a = p.hw[bb + R];
+      for (int sft = 1; sft <= a; ++sft) e &= (rw >> sft) & (rw << sft);
+      interior &= e;
+    }
 #pragma unroll
-  for (int k = 0; k < 64; ++k) {
-    const int i = kZig[k];
-    const float qv = __fmul_rn(d[i >> 3][i & 7], p.rq[i]);
-    const int c = __float2int_rz(__fadd_rn(qv, copysignf(0.5f, qv)));
-    if (c != 0) nz |= 1ull << k;
-    if (k & 1) wout[k >> 1] |= (uint32_t)(c & 0xffff) << 16;
-    else wout[k >> 1] = (uint32_t)(c & 0xffff);
+    for (int x = 0; x < 8; ++x) {
+      const bool lab = (m >> (8 + x)) & 1u, in = (interior >> (8 + x)) & 1u;
+      const int grey = lab ? (in ? p.interior : p.border) : p.background;
+      d[y][x] = __fsub_rn((float)grey, 128.0f);
+    }
   }
-  uint4* dst = reinterpret_cast<uint4*>(p.blocks + (size_t)b * 64);
-#pragma unroll
-  for (int k = 0; k < 8; ++k) dst[k] = make_uint4(wout[4 * k], wout[4 * k + 1], wout[4 * k + 2], wout[4 * k + 3]);
-  p.nz[b] = nz;
+  transform_quantise_store(d, p.rq, p.blocks + (size_t)b * 64, p.nz + b);
 }
 
 }  // namespace
@@ -136,6 +186,16 @@ cudaError_t launch_export_blocks(const ExportParams& p, cudaStream_t s) {
   const long long grid = (total + kExportThreads - 1) / kExportThreads;
   if (grid > 0x7fffffffLL) return cudaErrorInvalidValue;
   k_render_dct<<<(unsigned)grid, kExportThreads, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_export_seg_blocks(const ExportSegParams& p, cudaStream_t s) {
+  if (p.n <= 0 || p.w <= 0 || p.h <= 0 || (p.w & 7) || (p.h & 7) || p.radius < 0 || p.radius > 7 || !p.bits || !p.blocks || !p.nz)
+    return cudaErrorInvalidValue;
+  const long long total = (long long)p.n * (p.w >> 3) * (p.h >> 3);
+  const long long grid = (total + kExportThreads - 1) / kExportThreads;
+  if (grid > 0x7fffffffLL) return cudaErrorInvalidValue;
+  k_seg_render_dct<<<(unsigned)grid, kExportThreads, 0, s>>>(p);
   return cudaGetLastError();
 }
 

@@ -19,4 +19,19 @@ struct ExportParams {
 
 cudaError_t launch_export_blocks(const ExportParams& p, cudaStream_t s);
 
+// The same for the rendering of the RESULT: SegmentationRenderer of a {0,1} label image on a canvas of its own size
+// (host/nm03.hpp paintBits): labelled pixels in the interior grey, labelled pixels within `radius` (disc; outside the
+// image counts as unlabelled) of an unlabelled one in the border grey, everything else the background grey.
+struct ExportSegParams {
+  const uint32_t* bits;       // [n][h][wpr] the result mask, bit x%32 of word x/32 = pixel x (nm03_outputs.dilated_bits)
+  int n, w, h, wpr;           // w, h multiples of 8
+  int radius;                 // border radius, 0..7
+  int8_t hw[15];              // half-width of the border disc at row offset b (index b + radius)
+  uint8_t background, interior, border;
+  int16_t* blocks;
+  unsigned long long* nz;
+  float rq[64];
+};
+cudaError_t launch_export_seg_blocks(const ExportSegParams& p, cudaStream_t s);
+
 }  // namespace nm03

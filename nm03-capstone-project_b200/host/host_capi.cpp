@@ -141,6 +141,35 @@ int nm03h_export_blocks_cpu(const void* px, int w, int h, int is_unsigned, int q
   } catch (const std::exception&) { return -1; }
 }
 
+// CPU statement of nm03_outputs.export_seg_blocks: SegmentationRenderer(label 1 = white, opacity, borderOpacity, radius)
+// over black on a canvas of the image's own size, then the same per-block steps; style3 receives the three greys
+// (background, interior, border) a caller hands to the GPU
+int nm03h_export_seg_blocks_cpu(const void* lab, int lab_is_bits, int w, int h, float opacity, float border_opacity, int radius,
+                                int quality, int16_t* blocks, uint64_t* nz, uint8_t* style3) {
+  try {
+    if (w <= 0 || h <= 0 || (w & 7) || (h & 7)) return -3;
+    auto img = lab_is_bits ? nm03::Image::viewBits((const uint32_t*)lab, w, h) : nm03::Image::view(lab, w, h, nm03::TYPE_UINT8);
+    nm03::LabelColors colors;
+    colors[1] = nm03::Color::White();
+    auto rti = nm03::RenderToImage::create(nm03::Color::Black(), w, h);
+    rti->connect(nm03::SegmentationRenderer::create(colors, opacity, border_opacity, radius)->addInputData(img));
+    rti->update();
+    const uint8_t* plane = rti->getOutputData<nm03::Image>(0)->greyPlane();
+    if (!plane) return -2;
+    const nm03::jpeg::Tables tb = nm03::jpeg::make_tables(quality);
+    size_t b = 0;
+    for (int by = 0; by < h; by += 8)
+      for (int bx = 0; bx < w; bx += 8, ++b)
+        nm03::jpeg::block_coefficients(plane + (size_t)by * w + bx, (size_t)w, tb.rq[0], blocks + 64 * b, nz + b);
+    if (style3) {
+      style3[0] = 0;
+      style3[1] = nm03::SegmentationRenderer::blend(0, 1.0f, opacity);
+      style3[2] = nm03::SegmentationRenderer::blend(0, 1.0f, border_opacity);
+    }
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
 // the reciprocal quantiser (64 floats, natural order) a caller hands to nm03_outputs.export_rq for a JPEG quality
 void nm03h_jpeg_rq(int quality, float* rq64) {
   const nm03::jpeg::Tables tb = nm03::jpeg::make_tables(quality);

@@ -688,6 +688,11 @@ class SegmentationRenderer : public Renderer {
     for (auto& kv : colors_) if (kv.second.r != kv.second.g || kv.second.g != kv.second.b) return false;
     return true;
   }
+  // one channel of a label colour blended over a canvas byte with an opacity: the arithmetic of paint() (callers that
+  // have the GPU render, nm03_outputs.export_seg_blocks, need the resulting greys)
+  static uint8_t blend(uint8_t canvas, float colour, float opacity) {
+    return (uint8_t)(int)(canvas * (1 - opacity) + 255.0f * colour * opacity + 0.5f);
+  }
  private:
   // The driver's case — a {0,1} label image on a canvas of its own size — on bit planes: the labelled pixels as one bit
   // each (taken as they are from a bit-packed image, else packed here, giving up if any other label occurs), the

@@ -237,11 +237,18 @@ struct BufRing {
   }
 };
 
+// SegmentationRenderer::create(labelColors, 0.6f, 1.0f, 2) with label 1 = white over black, main_sequential.cpp:255-261
+constexpr float kSegOpacity = 0.6f, kSegBorderOpacity = 1.0f;
+constexpr int kSegBorderRadius = 2;
+const nm03_export_style kSegStyle = {0, nm03::SegmentationRenderer::blend(0, 1.0f, kSegOpacity),
+                                     nm03::SegmentationRenderer::blend(0, 1.0f, kSegBorderOpacity), kSegBorderRadius};
+
 // mask: uint8 labels, or (bits = true) the bit-packed words of nm03_outputs.dilated_bits
 // blocks / nz: the original's quantised 8x8 blocks from the GPU (nm03_outputs.export_blocks), or null: rendered and
 // transformed here
 void exportSlice(const fs::path& dir, const std::string& file, const int16_t* raw, bool is_unsigned, const void* mask, bool bits, int w, int h,
-                 const int16_t* blocks = nullptr, const uint64_t* nz = nullptr) {
+                 const int16_t* blocks = nullptr, const uint64_t* nz = nullptr, const int16_t* seg_blocks = nullptr,
+                 const uint64_t* seg_nz = nullptr) {
   using namespace nm03;
   const std::string stem = fs::path(file).stem().string();
   // views of the pinned staging buffers (they outlive this call): no copies, and the segmentation renderer works on the
@@ -251,22 +258,27 @@ void exportSlice(const fs::path& dir, const std::string& file, const int16_t* ra
   LabelColors colors;
   colors[1] = Color::White();
   auto rti = RenderToImage::create(Color::Black(), 512, 512);  // main_sequential.cpp:258
-  if (blocks && w == 512 && h == 512) {
-    // the canvas is the slice's own size, so the GPU's blocks are the rendering's: only the entropy coding is left
-    const std::vector<uint8_t> b = jpeg::encode_blocks(blocks, nz, w, h, ImageFileExporter::kDefaultJpegQuality);
-    const std::string path = (dir / (stem + "_original.jpg")).string();
+  // the canvas is the slice's own size, so the GPU's blocks are the rendering's: only the entropy coding is left
+  auto write_blocks = [&](const int16_t* zz, const uint64_t* map, const char* suffix) {
+    const std::vector<uint8_t> b = jpeg::encode_blocks(zz, map, w, h, ImageFileExporter::kDefaultJpegQuality);
+    const std::string path = (dir / (stem + suffix)).string();
     FILE* f = std::fopen(path.c_str(), "wb");
     if (!f) throw Exception("cannot write " + path);
     const size_t nw = std::fwrite(b.data(), 1, b.size(), f);
     std::fclose(f);
     if (nw != b.size()) throw Exception("short write " + path);
+  };
+  const bool canvas_is_slice = w == 512 && h == 512;
+  if (blocks && canvas_is_slice) {
+    write_blocks(blocks, nz, "_original.jpg");
   } else {
     rti->connect(ImageRenderer::create()->addInputData(orig));
     rti->update();
     ImageFileExporter::create((dir / (stem + "_original.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
   }
+  if (seg_blocks && canvas_is_slice) { write_blocks(seg_blocks, seg_nz, "_processed.jpg"); return; }
   rti->removeAllRenderers();
-  rti->connect(SegmentationRenderer::create(colors, 0.6f, 1.0f, 2)->addInputData(seg));
+  rti->connect(SegmentationRenderer::create(colors, kSegOpacity, kSegBorderOpacity, kSegBorderRadius)->addInputData(seg));
   rti->update();
   ImageFileExporter::create((dir / (stem + "_processed.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
 }
@@ -353,7 +365,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     // quantised JPEG blocks: 128 bytes of coefficients + an 8-byte map per 8x8 block, behind the masks
     const bool gpu_blocks = opt.do_export && !opt.cpu_dct && w == 512 && h == 512;
     const size_t nblk = (size_t)(w / 8) * (h / 8), masks_end = (m * mask_bytes + 63) & ~(size_t)63;
-    out.reserve(masks_end + (gpu_blocks ? m * nblk * 136 : 0));
+    const bool gpu_seg_blocks = gpu_blocks && !opt.byte_masks;   // the result's rendering too (it is made from the bit-packed mask)
+    out.reserve(masks_end + (gpu_blocks ? m * nblk * 136 : 0) + (gpu_seg_blocks ? m * nblk * 136 : 0));
     nm03_outputs o = {};
     if (opt.byte_masks) o.dilated = (uint8_t*)out.p;
     else o.dilated_bits = (uint32_t*)out.p;
@@ -362,6 +375,11 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       o.export_blocks = (int16_t*)((uint8_t*)out.p + masks_end);
       o.export_nz = (uint64_t*)((uint8_t*)out.p + masks_end + m * nblk * 128);
       o.export_rq = tables.rq[0];
+    }
+    if (gpu_seg_blocks) {
+      o.export_seg_blocks = (int16_t*)((uint8_t*)out.p + masks_end + m * nblk * 136);
+      o.export_seg_nz = (uint64_t*)((uint8_t*)out.p + masks_end + m * nblk * 136 + m * nblk * 128);
+      o.export_seg_style = &kSegStyle;
     }
     std::vector<int> status(m, 0);
     const int rc = nm03_process_batch(ctx, gpu, in.p, m, w, h, &params, nullptr, 0, &o, status.data());
@@ -397,6 +415,8 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
       const bool is_unsigned = params.input_unsigned != 0, byte_masks = opt.byte_masks;
       const int16_t* blk_p = o.export_blocks;
       const uint64_t* nz_p = o.export_nz;
+      const int16_t* sblk_p = o.export_seg_blocks;
+      const uint64_t* snz_p = o.export_seg_nz;
       Totals* totp = &tot;
       BufRing* ringp = &ring;
       Pool* pool = g_pool;
@@ -406,7 +426,7 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
         try {
           exportSlice(outdir, names[j], (const int16_t*)((const uint8_t*)in_p + j * npx * 2), is_unsigned,
                       (const uint8_t*)out_p + j * mask_bytes, !byte_masks, w, h, blk_p ? blk_p + j * nblk * 64 : nullptr,
-                      nz_p ? nz_p + j * nblk : nullptr);
+                      nz_p ? nz_p + j * nblk : nullptr, sblk_p ? sblk_p + j * nblk * 64 : nullptr, snz_p ? snz_p + j * nblk : nullptr);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(totp->log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -419,7 +439,9 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
         try {
           exportSlice(outdir, files[idx[j]], (const int16_t*)((uint8_t*)in.p + j * npx * 2), params.input_unsigned,
                       (const uint8_t*)out.p + j * mask_bytes, !opt.byte_masks, w, h,
-                      o.export_blocks ? o.export_blocks + j * nblk * 64 : nullptr, o.export_nz ? o.export_nz + j * nblk : nullptr);
+                      o.export_blocks ? o.export_blocks + j * nblk * 64 : nullptr, o.export_nz ? o.export_nz + j * nblk : nullptr,
+                      o.export_seg_blocks ? o.export_seg_blocks + j * nblk * 64 : nullptr,
+                      o.export_seg_nz ? o.export_seg_nz + j * nblk : nullptr);
         } catch (const std::exception& e) {
           std::lock_guard<std::mutex> lk(tot.log);
           std::cerr << "Error in export stage: " << e.what() << std::endl;
@@ -472,7 +494,7 @@ int runBatch(Options opt) {
       rings.back()->sets.back()->in.reserve((size_t)opt.batch * 512 * 512 * 2);
       // masks (at most a byte per pixel) and, with export, the original's JPEG blocks from the GPU (136 bytes per 8x8 block)
       rings.back()->sets.back()->out.reserve((size_t)opt.batch * 512 * 512 + 64 +
-                                             (opt.do_export && !opt.cpu_dct ? (size_t)opt.batch * 4096 * 136 : 0));
+                                             (opt.do_export && !opt.cpu_dct ? (size_t)opt.batch * 4096 * 136 * 2 : 0));
     }
   }
   for (int g = 0; g < n_gpus_used; ++g) {
@@ -483,12 +505,18 @@ int runBatch(Options opt) {
     nm03_params params;
     nm03_default_params(&params);
     nm03_outputs o = {};
-    o.dilated = (uint8_t*)out.p;
+    if (opt.byte_masks || !opt.do_export) o.dilated = (uint8_t*)out.p;
+    else o.dilated_bits = (uint32_t*)out.p;
     static const nm03::jpeg::Tables warm_tables = nm03::jpeg::make_tables(nm03::ImageFileExporter::kDefaultJpegQuality);
     if (opt.do_export && !opt.cpu_dct) {   // as the feeders will ask for it, so that the staging is sized and the kernels are loaded
       o.export_blocks = (int16_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64);
       o.export_nz = (uint64_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 128);
       o.export_rq = warm_tables.rq[0];
+      if (!opt.byte_masks) {
+        o.export_seg_blocks = (int16_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 136);
+        o.export_seg_nz = (uint64_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 136 + (size_t)m * 4096 * 128);
+        o.export_seg_style = &kSegStyle;
+      }
     }
     if (nm03_process_batch(ctx, g, in.p, m, 512, 512, &params, nullptr, 0, &o, nullptr) != NM03_OK) {
       std::cerr << "Fatal error: " << nm03_last_error() << std::endl;

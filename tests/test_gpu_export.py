@@ -78,6 +78,54 @@ def test_blocks_value_ranges_sizes_and_async(lib, ctx, host):
             np.testing.assert_array_equal(res["export_nz"][i], nz)
 
 
+@pytest.mark.parametrize("radius,opacity,border_opacity", [(2, 0.6, 1.0), (0, 0.5, 0.5), (1, 0.3, 0.9), (3, 0.6, 1.0), (7, 0.8, 0.4)])
+def test_result_blocks_equal_the_host_renderer(lib, ctx, host, radius, opacity, border_opacity):
+    """export_seg_blocks: SegmentationRenderer's rendering of the dilated mask, transformed and quantised on the GPU."""
+    raws = np.stack([cm.phantom(512, 512, 2, i) for i in range(3)] + [cm.phantom(512, 512, 5, 1, kind="lowcontrast")])
+    n, h, w = raws.shape
+    nb = (h // 8) * (w // 8)
+    style3 = np.zeros(3, np.uint8)
+    exp = []
+    quality = 75
+    # the greys of the style come from the host renderer's own arithmetic
+    dummy_b, dummy_n = np.zeros((nb, 64), np.int16), np.zeros(nb, np.uint64)
+    assert host.nm03h_export_seg_blocks_cpu(np.zeros((h, w), np.uint8).ctypes.data_as(C.c_void_p), 0, w, h, C.c_float(opacity),
+                                            C.c_float(border_opacity), radius, quality, dummy_b.ctypes.data_as(C.c_void_p),
+                                            dummy_n.ctypes.data_as(C.c_void_p), style3.ctypes.data_as(C.c_void_p)) == 0
+    style = lib.ExportStyle(int(style3[0]), int(style3[1]), int(style3[2]), radius)
+    res = ctx.process_batch(raws, lib.default_params(dilate_size=5), want=("dilated_bits", "export"),
+                            out={"export_rq": _rq(host, quality), "export_seg_style": style})
+    assert res["dilated_bits"].any()
+    for i in range(n):
+        blocks, nz = np.zeros((nb, 64), np.int16), np.zeros(nb, np.uint64)
+        bits = np.ascontiguousarray(res["dilated_bits"][i])
+        assert host.nm03h_export_seg_blocks_cpu(bits.ctypes.data_as(C.c_void_p), 1, w, h, C.c_float(opacity), C.c_float(border_opacity),
+                                                radius, quality, blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p),
+                                                None) == 0
+        np.testing.assert_array_equal(res["export_seg_blocks"][i], blocks, err_msg=f"slice {i}")
+        np.testing.assert_array_equal(res["export_seg_nz"][i], nz, err_msg=f"slice {i}")
+        ob, on = _cpu_blocks(host, raws[i], quality)                      # the original's blocks come with them
+        np.testing.assert_array_equal(res["export_blocks"][i], ob)
+
+
+def test_result_blocks_masks_at_the_image_border(lib, ctx, host):
+    """A grown region that runs into the image border (everything in range): border pixels along the edge, ragged sizes."""
+    raws = np.full((2, 104, 136), 1500, np.int16)                        # every pixel inside the region-growing window
+    raws[1, 40:60, 50:90] = 0
+    n, h, w = raws.shape
+    nb = (h // 8) * (w // 8)
+    style = lib.ExportStyle(0, 153, 255, 2)
+    res = ctx.process_batch(raws, want=("dilated_bits", "export"), out={"export_rq": _rq(host, 75), "export_seg_style": style})
+    assert lib.unpack_bits(res["dilated_bits"], w).mean() > 0.5
+    for i in range(n):
+        blocks, nz = np.zeros((nb, 64), np.int16), np.zeros(nb, np.uint64)
+        bits = np.ascontiguousarray(res["dilated_bits"][i])
+        assert host.nm03h_export_seg_blocks_cpu(bits.ctypes.data_as(C.c_void_p), 1, w, h, C.c_float(0.6), C.c_float(1.0), 2, 75,
+                                                blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p), None) == 0
+        np.testing.assert_array_equal(res["export_seg_blocks"][i], blocks)
+        np.testing.assert_array_equal(res["export_seg_nz"][i], nz)
+
+
 def test_blocks_need_whole_blocks_and_all_three_pointers(lib, ctx, host):
     with pytest.raises(lib.Nm03Error) as e:
         ctx.process_batch(np.zeros((1, 100, 132), np.int16), want=("dilated", "export"), out={"export_rq": _rq(host, 75)})

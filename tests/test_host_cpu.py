@@ -402,3 +402,28 @@ def test_jpeg_from_blocks_equals_direct_encoder(host, unsigned, shape, quality):
     from PIL import Image
     dec = np.asarray(Image.open(io.BytesIO(out[:n2].tobytes())))
     assert dec.shape == shape and np.abs(dec.astype(int) - grey.astype(int)).mean() < (8 if min(w, h) >= 100 else 45)   # noise images lose more
+
+
+def test_jpeg_from_result_blocks_equals_direct_encoder(host):
+    import scipy.ndimage as ndi
+    host.nm03h_jpeg_from_blocks.restype = C.c_long
+    h, w = 256, 320
+    rng = np.random.default_rng(9)
+    lab = (ndi.gaussian_filter(rng.random((h, w)), 4) > 0.5).astype(np.uint8)
+    lab[:5, 30:90] = 1
+    grey = np.zeros((h, w), np.uint8)
+    assert host.nm03h_render_segmentation_grey(lab.ctypes.data_as(C.c_void_p), 0, w, h, w, h, C.c_float(0.6), C.c_float(1.0), 2,
+                                               grey.ctypes.data_as(C.c_void_p)) == 0
+    direct = np.zeros(w * h + 4096, np.uint8)
+    n1 = host.nm03h_jpeg_encode(grey.ctypes.data_as(C.c_void_p), w, h, 1, 75, direct.ctypes.data_as(C.c_void_p), C.c_long(direct.size))
+    nb = (w // 8) * (h // 8)
+    blocks, nz, style = np.zeros((nb, 64), np.int16), np.zeros(nb, np.uint64), np.zeros(3, np.uint8)
+    assert host.nm03h_export_seg_blocks_cpu(lab.ctypes.data_as(C.c_void_p), 0, w, h, C.c_float(0.6), C.c_float(1.0), 2, 75,
+                                            blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p),
+                                            style.ctypes.data_as(C.c_void_p)) == 0
+    assert style.tolist() == [0, 153, 255] and set(np.unique(grey)) <= {0, 153, 255}
+    out = np.zeros(direct.size, np.uint8)
+    n2 = host.nm03h_jpeg_from_blocks(blocks.ctypes.data_as(C.c_void_p), nz.ctypes.data_as(C.c_void_p), w, h, 75,
+                                     out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+    assert n1 > 0 and n1 == n2
+    np.testing.assert_array_equal(out[:n2], direct[:n1])
