@@ -44,6 +44,10 @@ struct Options {
   std::vector<int> gpus;
   int batch = 25, streams = 0, host_threads = 0;   // feeders per GPU, 0 = choose (see runBatch)
   bool do_export = true, dump_masks = false, lowcontrast = false;
+  // --gpu-seg: the RESULT's rendering, transform and quantisation on the GPU as well.  Off by default: its blocks double the
+  // bytes a batch brings back, and on one GPU + 16 cores that costs the feeders more than the host saves (20 100 vs 21 800
+  // slices/s with 3 feeders; all on the host: 15 300)
+  bool gpu_seg = false;
   bool cpu_dct = false;      // --cpu-dct: render, transform and quantise the original on the host (default: the GPU does, next to the pipeline)
   bool byte_masks = false;   // --byte-masks: fetch the uint8 mask from the GPU instead of the bit-packed one (8x the bytes over the link)
   int patients = 20, slices = 24, size = 512;
@@ -365,7 +369,7 @@ void processPatient(nm03_ctx* ctx, int gpu, const Options& opt, const std::strin
     // quantised JPEG blocks: 128 bytes of coefficients + an 8-byte map per 8x8 block, behind the masks
     const bool gpu_blocks = opt.do_export && !opt.cpu_dct && w == 512 && h == 512;
     const size_t nblk = (size_t)(w / 8) * (h / 8), masks_end = (m * mask_bytes + 63) & ~(size_t)63;
-    const bool gpu_seg_blocks = gpu_blocks && !opt.byte_masks;   // the result's rendering too (it is made from the bit-packed mask)
+    const bool gpu_seg_blocks = gpu_blocks && !opt.byte_masks && opt.gpu_seg;   // the result's rendering too (it is made from the bit-packed mask)
     out.reserve(masks_end + (gpu_blocks ? m * nblk * 136 : 0) + (gpu_seg_blocks ? m * nblk * 136 : 0));
     nm03_outputs o = {};
     if (opt.byte_masks) o.dilated = (uint8_t*)out.p;
@@ -494,7 +498,7 @@ int runBatch(Options opt) {
       rings.back()->sets.back()->in.reserve((size_t)opt.batch * 512 * 512 * 2);
       // masks (at most a byte per pixel) and, with export, the original's JPEG blocks from the GPU (136 bytes per 8x8 block)
       rings.back()->sets.back()->out.reserve((size_t)opt.batch * 512 * 512 + 64 +
-                                             (opt.do_export && !opt.cpu_dct ? (size_t)opt.batch * 4096 * 136 * 2 : 0));
+                                             (opt.do_export && !opt.cpu_dct ? (size_t)opt.batch * 4096 * 136 * (opt.gpu_seg ? 2 : 1) : 0));
     }
   }
   for (int g = 0; g < n_gpus_used; ++g) {
@@ -512,7 +516,7 @@ int runBatch(Options opt) {
       o.export_blocks = (int16_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64);
       o.export_nz = (uint64_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 128);
       o.export_rq = warm_tables.rq[0];
-      if (!opt.byte_masks) {
+      if (!opt.byte_masks && opt.gpu_seg) {
         o.export_seg_blocks = (int16_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 136);
         o.export_seg_nz = (uint64_t*)((uint8_t*)out.p + (size_t)m * 512 * 512 + 64 + (size_t)m * 4096 * 136 + (size_t)m * 4096 * 128);
         o.export_seg_style = &kSegStyle;
@@ -660,6 +664,7 @@ int main(int argc, char** argv) {
     else if (a == "--dump-masks") opt.dump_masks = true;
     else if (a == "--byte-masks") opt.byte_masks = true;
     else if (a == "--cpu-dct") opt.cpu_dct = true;
+    else if (a == "--gpu-seg") opt.gpu_seg = true;
     else if (a == "--test-pipeline") opt.test_file = val();
     else if (a == "--make-dataset") opt.make_dataset = val();
     else if (a == "--patients") opt.patients = std::atoi(val().c_str());

@@ -136,8 +136,8 @@ def test_driver_files_identical_with_and_without_gpu_blocks(tmp_path):
     base = tmp_path / "data" / "Brain-Tumor-Progression" / "T1-Post-Combined-P001-P020"
     subprocess.check_call([DRIVER, "--make-dataset", str(base), "--patients", "2", "--slices", "6", "--size", "512"])
     outs = {}
-    for name, extra in (("gpu", []), ("cpu", ["--cpu-dct"])):
+    for name, extra in (("gpu", []), ("gpu_seg", ["--gpu-seg"]), ("cpu", ["--cpu-dct"])):
         out = tmp_path / name
         subprocess.run([DRIVER, "--mode", "parallel", "--data", str(base), "--out", str(out)] + extra, capture_output=True, text=True, check=True)
         outs[name] = {str(p.relative_to(out)): hashlib.md5(p.read_bytes()).hexdigest() for p in sorted(out.rglob("*.jpg"))}
-    assert len(outs["gpu"]) == 24 and outs["gpu"] == outs["cpu"]
+    assert len(outs["gpu"]) == 24 and outs["gpu"] == outs["cpu"] and outs["gpu_seg"] == outs["cpu"]
