@@ -170,6 +170,17 @@ int nm03h_export_seg_blocks_cpu(const void* lab, int lab_is_bits, int w, int h, 
   } catch (const std::exception&) { return -1; }
 }
 
+// the driver's one-step export of the result: SegmentationRenderer(label 1 = white, ...) over black + baseline JPEG, from the bit-packed mask
+long nm03h_segmentation_jpeg_from_bits(const uint32_t* bits, int w, int h, float opacity, float border_opacity, int radius, int quality,
+                                       uint8_t* out, long cap) {
+  try {
+    const std::vector<uint8_t> b = nm03::encodeSegmentationJpeg(bits, w, h, 1.0f, opacity, border_opacity, radius, 0, quality);
+    if ((long)b.size() > cap) return -(long)b.size();
+    std::memcpy(out, b.data(), b.size());
+    return (long)b.size();
+  } catch (const std::exception&) { return 0; }
+}
+
 // the reciprocal quantiser (64 floats, natural order) a caller hands to nm03_outputs.export_rq for a JPEG quality
 void nm03h_jpeg_rq(int quality, float* rq64) {
   const nm03::jpeg::Tables tb = nm03::jpeg::make_tables(quality);

@@ -91,7 +91,8 @@ struct BitWriter {
       const uint32_t w = (uint32_t)(acc >> (nbits - 32));
       nbits -= 32;
       if (((w & ~(w + 0x01010101u)) & 0x80808080u) == 0) {   // no byte of w is 0xFF
-        p[0] = (uint8_t)(w >> 24); p[1] = (uint8_t)(w >> 16); p[2] = (uint8_t)(w >> 8); p[3] = (uint8_t)w;
+        const uint32_t be = __builtin_bswap32(w);   // most significant byte first, one store
+        std::memcpy(p, &be, 4);
         p += 4;
       } else {
         for (int sh = 24; sh >= 0; sh -= 8) {
@@ -247,11 +248,24 @@ inline Tables make_tables(int quality) {
 
 namespace detail {
 
+inline int bitsize(int v) { const unsigned a = (unsigned)(v < 0 ? -v : v); return a ? 32 - __builtin_clz(a) : 0; }
+
 struct HuffSet {
   Huff dc[2], ac[2];
+  // luma AC symbols with their value bits already appended, for the small values nearly every coefficient has:
+  // fast[run][v + 128] = (bits << 8) | length for -127 <= v <= 127, v != 0 (length <= 16 + 7)
+  uint32_t fast[16][256];
   HuffSet() {
     dc[0].build(kDcLumaBits, kDcVals); dc[1].build(kDcChromaBits, kDcVals);
     ac[0].build(kAcLumaBits, kAcLumaVals); ac[1].build(kAcChromaBits, kAcChromaVals);
+    for (int run = 0; run < 16; ++run)
+      for (int v = -127; v <= 127; ++v) {
+        if (v == 0) { fast[run][128] = 0; continue; }
+        const int sz = bitsize(v), rs = (run << 4) | sz;
+        const uint32_t vb = (uint32_t)(v < 0 ? v - 1 : v) & ((1u << sz) - 1u);
+        fast[run][v + 128] = ((((uint32_t)ac[0].code[rs] << sz) | vb) << 8) | (uint32_t)(ac[0].len[rs] + sz);
+      }
+    for (int run = 0; run < 16; ++run) fast[run][0] = 0;   // (-128 is not tabulated)
   }
 };
 inline const HuffSet& huffman() {   // built once; initialisation of a function-local static is thread-safe
@@ -292,11 +306,10 @@ inline void write_headers(std::vector<uint8_t>& o, int width, int height, int ch
   }
 }
 
-inline int bitsize(int v) { const unsigned a = (unsigned)(v < 0 ? -v : v); return a ? 32 - __builtin_clz(a) : 0; }
-
 // One block's symbols: the DC difference, then (run, size) symbols of the AC terms in zigzag order; code and value bits go
 // out together.  zz = the 64 quantised coefficients in zigzag order, nz = bit k set iff zz[k] != 0 (bit 0 is ignored).
-inline void put_block(BitWriter& bw, const Huff& hdc, const Huff& hac, const int16_t* zz, uint64_t nz, int& pred) {
+inline void put_block(BitWriter& bw, const Huff& hdc, const Huff& hac, const int16_t* zz, uint64_t nz, int& pred,
+                      const uint32_t (*fast)[256] = nullptr) {
   const int diff = zz[0] - pred;
   pred = zz[0];
   {
@@ -313,6 +326,11 @@ inline void put_block(BitWriter& bw, const Huff& hdc, const Huff& hac, const int
     prev = i;
     while (run > 15) { bw.put(hac.code[0xF0], hac.len[0xF0]); run -= 16; }
     const int v = zz[i];
+    if (fast && (unsigned)(v + 127) <= 254u) {   // one look-up: code and value bits together
+      const uint32_t e = fast[run][v + 128];
+      bw.put(e >> 8, (int)(e & 0xFFu));
+      continue;
+    }
     const int sz = bitsize(v), rs = (run << 4) | sz;
     const uint32_t vb = (uint32_t)(v < 0 ? v - 1 : v) & ((1u << sz) - 1u);
     bw.put(((uint32_t)hac.code[rs] << sz) | vb, hac.len[rs] + sz);
@@ -343,7 +361,7 @@ inline std::vector<uint8_t> encode_blocks(const int16_t* zz, const uint64_t* nz,
   for (int by = 0; by < height; by += 8) {
     if (o.size() - pos < (size_t)blocks_per_row * kWorstBlock + 64) o.resize(pos + (size_t)blocks_per_row * kWorstBlock * 2 + 64);
     bw.p = o.data() + pos;
-    for (int bx = 0; bx < blocks_per_row; ++bx, ++b) put_block(bw, hf.dc[0], hf.ac[0], zz + 64 * b, nz[b], pred);
+    for (int bx = 0; bx < blocks_per_row; ++bx, ++b) put_block(bw, hf.dc[0], hf.ac[0], zz + 64 * b, nz[b], pred, hf.fast);
     pos = (size_t)(bw.p - o.data());
   }
   if (o.size() - pos < 32) o.resize(pos + 32);
@@ -369,7 +387,16 @@ inline void block_coefficients(const uint8_t* px, size_t stride, const float* rq
 #endif
   uint64_t m = 0;
   for (int i = 0; i < 64; ++i) { zz[kUnzigzag[i]] = (int16_t)q[i]; }
+#if defined(__SSE2__)
+  for (int k = 0; k < 4; ++k) {
+    const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i*>(zz + 16 * k));
+    const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i*>(zz + 16 * k + 8));
+    const int zero16 = _mm_movemask_epi8(_mm_cmpeq_epi8(_mm_packs_epi16(a, b), _mm_setzero_si128()));
+    m |= (uint64_t)(uint16_t)~zero16 << (16 * k);
+  }
+#else
   for (int i = 0; i < 64; ++i) m |= (uint64_t)(zz[i] != 0) << i;
+#endif
   *nz = m;
 }
 

@@ -845,6 +845,124 @@ class ImageFileExporter : public Typed<ImageFileExporter> {
   int quality_ = kDefaultJpegQuality;
 };
 
+// The driver's second export in one step: SegmentationRenderer(label 1 = colour, opacity, borderOpacity, borderRadius) of
+// a bit-packed {0,1} label image over a uniform grey background on a canvas of the image's own size, written as the
+// baseline JPEG ImageFileExporter would write from that canvas — without the canvas.  A rendered mask is flat almost
+// everywhere, and a flat block's only non-zero coefficient is known from its grey: blocks without a labelled pixel, and
+// blocks that lie wholly in the interior, cost a few loads and six bits; only blocks the region's outline runs through
+// are rendered, transformed and quantised.  Same bytes as the canvas path (tests/test_host_cpu.py).  w and h multiples
+// of 8; bits as in nm03_outputs.dilated_bits.
+inline std::vector<uint8_t> encodeSegmentationJpeg(const uint32_t* bits, int w, int h, float colour, float opacity, float borderOpacity,
+                                                   int borderRadius, uint8_t background, int quality) {
+  using namespace jpeg;
+  using namespace jpeg::detail;
+  if (w <= 0 || h <= 0 || (w & 7) || (h & 7)) throw Exception("encodeSegmentationJpeg: width and height must be multiples of 8");
+  const int wpr = (w + 31) / 32, R = std::max(0, std::min(borderRadius, 15));
+  const uint8_t grey_in = SegmentationRenderer::blend(background, colour, opacity);
+  const uint8_t grey_bd = SegmentationRenderer::blend(background, colour, borderOpacity);
+  // interior = the labelled pixels eroded by the border disc, everything outside the image unlabelled (paintBits)
+  int hw[31];
+  for (int b = -R; b <= R; ++b) { int a = 0; while ((a + 1) * (a + 1) + b * b <= R * R) ++a; hw[b + R] = a; }
+  std::vector<uint32_t> rowe((size_t)(R + 1) * h * wpr);   // rowe[a][y][k]: row y eroded horizontally by half-width a
+  for (int y = 0; y < h; ++y) {
+    const uint32_t* row = bits + (size_t)y * wpr;
+    for (int k = 0; k < wpr; ++k) {
+      if (!row[k]) continue;                                   // (the planes start out zero)
+      const uint32_t lo = k > 0 ? row[k - 1] : 0u, hi = k + 1 < wpr ? row[k + 1] : 0u;
+      uint32_t acc = row[k];
+      rowe[(size_t)y * wpr + k] = acc;
+      for (int a = 1; a <= R; ++a) {
+        acc &= ((row[k] >> a) | (hi << (32 - a))) & ((row[k] << a) | (lo >> (32 - a)));
+        rowe[((size_t)a * h + y) * wpr + k] = acc;
+      }
+    }
+  }
+  std::vector<uint32_t> interior((size_t)h * wpr);
+  for (int y = 0; y < h; ++y)
+    for (int k = 0; k < wpr; ++k) {
+      uint32_t acc = bits[(size_t)y * wpr + k];
+      if (!acc) continue;
+      for (int b = -R; b <= R && acc; ++b) {
+        const int yy = y + b;
+        acc = (yy < 0 || yy >= h) ? 0u : (acc & rowe[((size_t)hw[b + R] * h + yy) * wpr + k]);
+      }
+      interior[(size_t)y * wpr + k] = acc;
+    }
+  const Tables tb = make_tables(quality);
+  const HuffSet& hf = huffman();
+  std::vector<uint8_t> o;
+  o.reserve((size_t)w * h / 16 + 1024);
+  write_headers(o, w, h, 1, tb.q);
+  auto flat_dc = [&](uint8_t g) {   // a flat block's DC term, as encode() computes it
+    const float qv = ((float)g - 128.0f) * 64.0f * tb.rq[0][0];
+    return (int16_t)(int)(qv + (qv >= 0.0f ? 0.5f : -0.5f));
+  };
+  const int16_t dc_bg = flat_dc(background), dc_in = flat_dc(grey_in);
+  // a flat block whose DC term equals its predecessor's: the code of size 0, then the end-of-block code
+  const int flat_same_len = hf.dc[0].len[0] + hf.ac[0].len[0x00];
+  const uint32_t flat_same_bits = ((uint32_t)hf.dc[0].code[0] << hf.ac[0].len[0x00]) | hf.ac[0].code[0x00];
+  const int bpr = w / 8;
+  size_t pos = o.size();
+  int pred = 0;
+  BitWriter bw(nullptr);
+  alignas(16) int16_t zz[64];
+  std::memset(zz, 0, sizeof(zz));
+  std::vector<uint32_t> any_w(wpr), all_w(wpr);
+  static const auto spread = [] {   // bit i of the index -> byte i = 1
+    std::vector<uint64_t> t(256);
+    for (int b = 0; b < 256; ++b) { uint64_t v = 0; for (int i = 0; i < 8; ++i) v |= (uint64_t)((b >> i) & 1) << (8 * i); t[b] = v; }
+    return t;
+  }();
+  for (int by = 0; by < h; by += 8) {
+    if (o.size() - pos < (size_t)bpr * kWorstBlock + 64) o.resize(pos + (size_t)bpr * kWorstBlock * 2 + 64);
+    bw.p = o.data() + pos;
+    const uint8_t* mrow[8];
+    const uint8_t* irow[8];
+    for (int y = 0; y < 8; ++y) {   // byte bx of a row's words = the eight pixels of block column bx (little-endian words)
+      mrow[y] = reinterpret_cast<const uint8_t*>(bits + (size_t)(by + y) * wpr);
+      irow[y] = reinterpret_cast<const uint8_t*>(interior.data() + (size_t)(by + y) * wpr);
+    }
+    // the eight rows of the block row folded word by word: a byte of any_w is zero where a block has no labelled pixel, a
+    // byte of all_w is 0xFF where every pixel of a block is an interior pixel (interior pixels are labelled)
+    for (int k = 0; k < wpr; ++k) {
+      uint32_t a = 0u, b = 0xFFFFFFFFu;
+      for (int y = 0; y < 8; ++y) { a |= bits[(size_t)(by + y) * wpr + k]; b &= interior[(size_t)(by + y) * wpr + k]; }
+      any_w[k] = a; all_w[k] = b;
+    }
+    const uint8_t* any_b = reinterpret_cast<const uint8_t*>(any_w.data());
+    const uint8_t* all_b = reinterpret_cast<const uint8_t*>(all_w.data());
+    for (int bx = 0; bx < bpr; ++bx) {
+      if (any_b[bx] == 0 || all_b[bx] == 0xFF) {
+        zz[0] = any_b[bx] == 0 ? dc_bg : dc_in;
+        if (zz[0] == pred) bw.put(flat_same_bits, flat_same_len);   // DC difference 0, then end of block
+        else put_block(bw, hf.dc[0], hf.ac[0], zz, 0, pred);
+        continue;
+      }
+      alignas(8) uint8_t px[64];
+      for (int y = 0; y < 8; ++y) {   // eight pixels at a time: the three pixel classes are disjoint, so the byte-wise products add without carries
+        const uint8_t m = mrow[y][bx], in = irow[y][bx];
+        const uint64_t row8 = spread[(uint8_t)~m] * background + spread[(uint8_t)(m & ~in)] * grey_bd + spread[in] * grey_in;
+        std::memcpy(px + 8 * y, &row8, 8);
+      }
+      bool flat = true;
+      for (int i = 1; i < 64 && flat; ++i) flat = px[i] == px[0];
+      alignas(16) int16_t bz[64];
+      uint64_t nz = 0;
+      if (flat) { std::memset(bz, 0, sizeof(bz)); bz[0] = flat_dc(px[0]); }   // e.g. a block of border pixels only
+      else block_coefficients(px, 8, tb.rq[0], bz, &nz);
+      put_block(bw, hf.dc[0], hf.ac[0], bz, nz, pred);
+    }
+    pos = (size_t)(bw.p - o.data());
+  }
+  if (o.size() - pos < 32) o.resize(pos + 32);
+  bw.p = o.data() + pos;
+  bw.flush();
+  pos = (size_t)(bw.p - o.data());
+  o.resize(pos);
+  o.push_back(0xFF); o.push_back(0xD9);  // EOI
+  return o;
+}
+
 // The 5-pane GUI of test_pipeline.cpp:148-158 needs a window system; it is left out (no graphics
 // stack on this box).  run() returns immediately so the export stage that follows still executes.
 class MultiViewWindow {

@@ -281,6 +281,18 @@ void exportSlice(const fs::path& dir, const std::string& file, const int16_t* ra
     ImageFileExporter::create((dir / (stem + "_original.jpg")).string())->connect(rti->getOutputData<Image>(0))->update();
   }
   if (seg_blocks && canvas_is_slice) { write_blocks(seg_blocks, seg_nz, "_processed.jpg"); return; }
+  if (bits && canvas_is_slice) {
+    // the result's rendering and its JPEG in one step from the bit-packed mask: no canvas, flat blocks short-cut
+    const std::vector<uint8_t> b = encodeSegmentationJpeg((const uint32_t*)mask, w, h, 1.0f, kSegOpacity, kSegBorderOpacity, kSegBorderRadius,
+                                                          0, ImageFileExporter::kDefaultJpegQuality);
+    const std::string path = (dir / (stem + "_processed.jpg")).string();
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) throw Exception("cannot write " + path);
+    const size_t nw = std::fwrite(b.data(), 1, b.size(), f);
+    std::fclose(f);
+    if (nw != b.size()) throw Exception("short write " + path);
+    return;
+  }
   rti->removeAllRenderers();
   rti->connect(SegmentationRenderer::create(colors, kSegOpacity, kSegBorderOpacity, kSegBorderRadius)->addInputData(seg));
   rti->update();

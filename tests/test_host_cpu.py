@@ -427,3 +427,48 @@ def test_jpeg_from_result_blocks_equals_direct_encoder(host):
                                      out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
     assert n1 > 0 and n1 == n2
     np.testing.assert_array_equal(out[:n2], direct[:n1])
+
+
+@pytest.mark.parametrize("radius,opacity,border_opacity", [(2, 0.6, 1.0), (0, 0.5, 0.5), (1, 0.3, 0.9), (3, 0.6, 1.0), (5, 0.8, 0.4)])
+@pytest.mark.parametrize("shape", [(512, 512), (104, 136), (64, 64)])
+def test_segmentation_jpeg_in_one_step_equals_render_then_encode(host, radius, opacity, border_opacity, shape):
+    """encodeSegmentationJpeg (no canvas, flat blocks short-cut) writes the bytes of SegmentationRenderer -> RenderToImage ->
+    ImageFileExporter on the same bit-packed mask."""
+    import scipy.ndimage as ndi
+    host.nm03h_segmentation_jpeg_from_bits.restype = C.c_long
+    h, w = shape
+    rng = np.random.default_rng(radius * 100 + w)
+    lab = (ndi.gaussian_filter(rng.random(shape), 3.0) > 0.5).astype(np.uint8)
+    lab[:7, 8:40] = 1                      # a region that runs into the image border
+    lab[h - 9:, w - 17:] = 1
+    lab[20:44, 16:48] = 1                  # whole blocks of interior pixels
+    lab[30, 30] = 0
+    wpr = (w + 31) // 32
+    padded = np.zeros((h, wpr * 32), np.uint8)
+    padded[:, :w] = lab
+    bits = np.packbits(padded, axis=1, bitorder="little").view(np.uint32).copy()
+    for quality in (75, 40):
+        grey = np.zeros(shape, np.uint8)
+        assert host.nm03h_render_segmentation_grey(bits.ctypes.data_as(C.c_void_p), 1, w, h, w, h, C.c_float(opacity),
+                                                   C.c_float(border_opacity), radius, grey.ctypes.data_as(C.c_void_p)) == 0
+        direct = np.zeros(w * h + 4096, np.uint8)
+        n1 = host.nm03h_jpeg_encode(grey.ctypes.data_as(C.c_void_p), w, h, 1, quality, direct.ctypes.data_as(C.c_void_p), C.c_long(direct.size))
+        out = np.zeros(direct.size, np.uint8)
+        n2 = host.nm03h_segmentation_jpeg_from_bits(bits.ctypes.data_as(C.c_void_p), w, h, C.c_float(opacity), C.c_float(border_opacity),
+                                                    radius, quality, out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+        assert n1 > 0 and n1 == n2
+        np.testing.assert_array_equal(out[:n2], direct[:n1])
+    # an empty and a full mask
+    for fill in (0, 0xFFFFFFFF):
+        b2 = np.full((h, wpr), fill, np.uint32)
+        if w % 32:
+            b2[:, -1] &= np.uint32((1 << (w % 32)) - 1)
+        grey = np.zeros(shape, np.uint8)
+        assert host.nm03h_render_segmentation_grey(b2.ctypes.data_as(C.c_void_p), 1, w, h, w, h, C.c_float(opacity), C.c_float(border_opacity),
+                                                   radius, grey.ctypes.data_as(C.c_void_p)) == 0
+        direct = np.zeros(w * h + 4096, np.uint8)
+        n1 = host.nm03h_jpeg_encode(grey.ctypes.data_as(C.c_void_p), w, h, 1, 75, direct.ctypes.data_as(C.c_void_p), C.c_long(direct.size))
+        out = np.zeros(direct.size, np.uint8)
+        n2 = host.nm03h_segmentation_jpeg_from_bits(b2.ctypes.data_as(C.c_void_p), w, h, C.c_float(opacity), C.c_float(border_opacity),
+                                                    radius, 75, out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+        assert n1 == n2 and np.array_equal(out[:n2], direct[:n1])
