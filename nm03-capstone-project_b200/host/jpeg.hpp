@@ -76,46 +76,54 @@ struct Huff {
   }
 };
 
-// Entropy-coded segment writer: bits collect in a 64-bit accumulator and leave four bytes at a time;
-// a word without any 0xFF byte (nearly all of them) is stored whole, the others byte by byte with
-// the 0x00 stuffing byte of T.81 B.1.1.5.  The caller keeps at least 16 bytes of room at `p`.
+// Entropy-coded segment writer: bits collect in a 64-bit accumulator and leave eight bytes at a time, when it is full;
+// eight bytes without any 0xFF among them (nearly all) are stored whole, the others byte by byte with the 0x00 stuffing
+// byte of T.81 B.1.1.5.  The caller keeps at least 32 bytes of room at `p`.
 struct BitWriter {
   uint8_t* p;
   uint64_t acc = 0;
-  int nbits = 0;
+  int free_bits = 64;   // unused low-order room in acc
   explicit BitWriter(uint8_t* dst) : p(dst) {}
-  inline void put(uint32_t bits, int len) {  // bits < 2^len, len <= 27
-    acc = (acc << len) | bits;
-    nbits += len;
-    if (nbits >= 32) {
-      const uint32_t w = (uint32_t)(acc >> (nbits - 32));
-      nbits -= 32;
-      if (((w & ~(w + 0x01010101u)) & 0x80808080u) == 0) {   // no byte of w is 0xFF
-        const uint32_t be = __builtin_bswap32(w);   // most significant byte first, one store
-        std::memcpy(p, &be, 4);
-        p += 4;
-      } else {
-        for (int sh = 24; sh >= 0; sh -= 8) {
-          const uint8_t b = (uint8_t)(w >> sh);
-          *p++ = b;
-          if (b == 0xFF) *p++ = 0;
-        }
+  inline void emit8(uint64_t v) {   // eight bytes, most significant first
+    if (((v & ~(v + 0x0101010101010101ull)) & 0x8080808080808080ull) == 0) {   // no byte of v is 0xFF
+      const uint64_t be = __builtin_bswap64(v);
+      std::memcpy(p, &be, 8);
+      p += 8;
+    } else {
+      for (int sh = 56; sh >= 0; sh -= 8) {
+        const uint8_t b = (uint8_t)(v >> sh);
+        *p++ = b;
+        if (b == 0xFF) *p++ = 0;
       }
     }
   }
-  inline void flush() {  // pad the last byte with 1-bits
-    while (nbits >= 8) {
-      const uint8_t b = (uint8_t)(acc >> (nbits - 8));
+  inline void put(uint32_t bits, int len) {  // bits < 2^len, 0 < len <= 32
+    if (len <= free_bits) {
+      acc = (acc << len) | bits;   // (a shift by 64 cannot occur: len <= 32)
+      free_bits -= len;
+    } else {                       // fill the accumulator with the leading bits, store it, keep the rest
+      const int rest = len - free_bits;
+      emit8(free_bits ? ((acc << free_bits) | (bits >> rest)) : acc);
+      acc = bits;                  // only the low `rest` bits count: the ones above them leave at the top before a store
+      free_bits = 64 - rest;
+    }
+  }
+  inline void flush() {  // whole bytes, then the last one padded with 1-bits
+    int nbits = 64 - free_bits;
+    const uint64_t v = nbits ? (acc << free_bits) : 0;   // left-aligned
+    int sh = 56;
+    for (; nbits >= 8; nbits -= 8, sh -= 8) {
+      const uint8_t b = (uint8_t)(v >> sh);
       *p++ = b;
       if (b == 0xFF) *p++ = 0;
-      nbits -= 8;
     }
     if (nbits > 0) {
-      const uint8_t b = (uint8_t)(((acc << (8 - nbits)) | (0xFFu >> nbits)) & 0xFFu);
+      const uint8_t b = (uint8_t)((v >> sh) | (0xFFu >> nbits));
       *p++ = b;
       if (b == 0xFF) *p++ = 0;
-      nbits = 0;
     }
+    acc = 0;
+    free_bits = 64;
   }
 };
 
