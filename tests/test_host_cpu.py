@@ -472,3 +472,24 @@ def test_segmentation_jpeg_in_one_step_equals_render_then_encode(host, radius, o
         n2 = host.nm03h_segmentation_jpeg_from_bits(b2.ctypes.data_as(C.c_void_p), w, h, C.c_float(opacity), C.c_float(border_opacity),
                                                     radius, 75, out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
         assert n1 == n2 and np.array_equal(out[:n2], direct[:n1])
+
+
+def test_jpeg_bit_writer_stuffing_on_noise_images(host):
+    """Noise at high quality fills the entropy-coded segment with 0xFF bytes (each followed by a stuffed 0x00): the 64-bit
+    accumulator of the writer must place them exactly, or PIL's decoder loses the stream."""
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    stuffed = 0
+    for q in (100, 95, 75, 30):
+        for _ in range(5):
+            h, w, ch = int(rng.integers(8, 200)), int(rng.integers(8, 300)), int(rng.choice([1, 3]))
+            img = rng.integers(0, 256, (h, w, ch) if ch == 3 else (h, w)).astype(np.uint8)
+            out = np.zeros(h * w * ch * 3 + 8192, np.uint8)
+            n = host.nm03h_jpeg_encode(img.ctypes.data_as(C.c_void_p), w, h, ch, q, out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+            assert n > 0
+            b = out[:n].tobytes()
+            stuffed += b[b.index(b"\xff\xda"):].count(b"\xff\x00")
+            dec = np.asarray(Image.open(io.BytesIO(b)))
+            assert dec.shape == img.shape
+            assert np.abs(dec.astype(int) - img.astype(int)).mean() < (4 if q == 100 else 60)
+    assert stuffed > 1000
