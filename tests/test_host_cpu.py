@@ -493,3 +493,44 @@ def test_jpeg_bit_writer_stuffing_on_noise_images(host):
             assert dec.shape == img.shape
             assert np.abs(dec.astype(int) - img.astype(int)).mean() < (4 if q == 100 else 60)
     assert stuffed > 1000
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_segmentation_jpeg_in_one_step_on_pathological_masks(host, seed):
+    """Single pixels, one-pixel lines, checkerboards, full blocks of border pixels, masks that fill whole block rows:
+    the short-cuts of encodeSegmentationJpeg must never change a byte."""
+    host.nm03h_segmentation_jpeg_from_bits.restype = C.c_long
+    rng = np.random.default_rng(1000 + seed)
+    h, w = int(rng.choice([64, 96, 128])), int(rng.choice([64, 104, 160]))
+    lab = np.zeros((h, w), np.uint8)
+    kind = seed % 6
+    if kind == 0:
+        lab[rng.integers(0, h, 40), rng.integers(0, w, 40)] = 1                      # isolated pixels
+    elif kind == 1:
+        lab[::3, :] = 1                                                               # one-pixel lines: everything is border
+    elif kind == 2:
+        lab[(np.add.outer(np.arange(h), np.arange(w)) % 2) == 0] = 1                  # checkerboard
+    elif kind == 3:
+        lab[8:16, :] = 1                                                              # exactly one block row
+        lab[24:48, 8:w - 8] = 1
+    elif kind == 4:
+        lab[:, :] = 1
+        lab[rng.integers(0, h, 5), rng.integers(0, w, 5)] = 0                         # full image with pin holes
+    else:
+        lab = (rng.random((h, w)) > 0.5).astype(np.uint8)                             # noise
+    radius = int(rng.integers(0, 6))
+    opacity, border_opacity = float(rng.choice([0.3, 0.6, 1.0])), float(rng.choice([0.5, 1.0]))
+    wpr = (w + 31) // 32
+    padded = np.zeros((h, wpr * 32), np.uint8)
+    padded[:, :w] = lab
+    bits = np.packbits(padded, axis=1, bitorder="little").view(np.uint32).copy()
+    grey = np.zeros((h, w), np.uint8)
+    assert host.nm03h_render_segmentation_grey(bits.ctypes.data_as(C.c_void_p), 1, w, h, w, h, C.c_float(opacity), C.c_float(border_opacity),
+                                               radius, grey.ctypes.data_as(C.c_void_p)) == 0
+    direct = np.zeros(w * h * 2 + 4096, np.uint8)
+    n1 = host.nm03h_jpeg_encode(grey.ctypes.data_as(C.c_void_p), w, h, 1, 75, direct.ctypes.data_as(C.c_void_p), C.c_long(direct.size))
+    out = np.zeros(direct.size, np.uint8)
+    n2 = host.nm03h_segmentation_jpeg_from_bits(bits.ctypes.data_as(C.c_void_p), w, h, C.c_float(opacity), C.c_float(border_opacity), radius, 75,
+                                                out.ctypes.data_as(C.c_void_p), C.c_long(out.size))
+    assert n1 > 0 and n1 == n2
+    np.testing.assert_array_equal(out[:n2], direct[:n1])
