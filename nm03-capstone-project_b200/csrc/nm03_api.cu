@@ -583,6 +583,11 @@ int check_export(const nm03_outputs* o, int w, int h) {
 int enqueue_export(Slot* s, cudaStream_t st, const void* d_slices, int n, int w, int h, int input_unsigned, const nm03_outputs* d_out) {
   if (!d_out->export_blocks) return NM03_OK;
   int rc;
+  // the block kernels load and store 16 bytes at a time (always true of the library's own staging; a device-pointer caller
+  // gets a clear refusal instead of a misaligned access)
+  if (((uintptr_t)d_slices & 15) || ((uintptr_t)d_out->export_blocks & 15) || ((uintptr_t)d_out->export_nz & 7) ||
+      (d_out->export_seg_blocks && (((uintptr_t)d_out->export_seg_blocks & 15) || ((uintptr_t)d_out->export_seg_nz & 7))))
+    return fail(NM03_ERR_UNSUPPORTED, "export blocks need 16-byte aligned slices and block arrays (8-byte aligned maps)");
   if ((rc = ensure(s, &s->win, &s->win_bytes, (size_t)n * sizeof(int2)))) return rc;
   nm03::ExportParams e;
   e.in = d_slices; e.n = n; e.w = w; e.h = h; e.input_unsigned = input_unsigned;
